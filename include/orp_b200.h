@@ -1,0 +1,188 @@
+/*
+ * orp_b200.h — C ABI of liborp_b200.so: the B200 (sm_100a) hot path of
+ * ithakis/Option-Replicating-Portfolio-with-Neural-Networks.
+ *
+ * Plain pointers and sizes only; no torch / C++ types cross this boundary.  Pointers named d_* are
+ * DEVICE pointers on the current CUDA device; everything else is host memory.  `stream` is a
+ * cudaStream_t passed as void* (NULL = default stream).  All device work is enqueued on `stream`
+ * and NOT synchronised.  The caller owns every buffer; nothing is retained after a call returns.
+ *
+ * Error convention: every function returns 0 on success and a negative code on failure
+ * (ORP_E_*); orp_last_error() returns the message of the calling thread's last failure.  The
+ * Python host layer turns ORP_E_VALUE into ValueError (what SciPy raises for a bad d / m,
+ * scipy/stats/_qmc.py:1771-1774, 1908-1915) and everything else into RuntimeError.
+ *
+ * The reference is pure Python, so "the reference interface each entry point replaces" is the
+ * Python/SciPy/Keras call named in the comment above each declaration (file:line under
+ * /root/reference unless it starts with scipy/).
+ */
+#ifndef ORP_B200_H
+#define ORP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORP_OK 0
+#define ORP_E_VALUE (-1)   /* bad argument (-> ValueError) */
+#define ORP_E_CUDA (-2)    /* CUDA runtime / launch failure (-> RuntimeError) */
+#define ORP_E_STATE (-3)   /* wrong device / missing set-up (-> RuntimeError) */
+
+#define ORP_SOBOL_BITS 30      /* scipy default, scipy/stats/_qmc.py:1780-1781 */
+#define ORP_SOBOL_MAXDIM 21201 /* scipy/stats/_sobol.pyi */
+#define ORP_SV_STRIDE 32       /* packed row: 30 direction numbers, word 30 = 0, word 31 = shift */
+
+int orp_version(void);
+const char* orp_last_error(void);
+
+/* ---------------------------------------------------------------- a-1  Sobol set-up (host, integer) */
+
+/* Replaces scipy.stats._sobol._initialize_v (called from qmc.Sobol.__init__, scipy/stats/_qmc.py:1793-1794
+ * <- Replicating_Portfolio.py:55).  poly[d], vinit[d][18]: Joe-Kuo data (SciPy ships them in
+ * _sobol_direction_numbers.npz).  v_out[d][bits]. */
+int orp_sobol_direction_numbers(const int64_t* poly, const int64_t* vinit, int d, int bits, uint32_t* v_out);
+
+/* Replaces qmc.Sobol._scramble + _cscramble (scipy/stats/_qmc.py:1812-1828): digital shift from
+ * shift_bits[d][bits] (LSB first) and left matrix scramble with ltm_bits[d][bits][bits] (lower triangle
+ * used, unit diagonal forced).  The random bits come from numpy.random.default_rng(seed).integers(2, ...)
+ * exactly as SciPy draws them.  sv_out[d][bits], shift_out[d]. */
+int orp_sobol_scramble(int d, int bits, const uint32_t* v, const uint32_t* shift_bits, const uint32_t* ltm_bits,
+                       uint32_t* sv_out, uint32_t* shift_out);
+
+/* Device-friendly packing (no reference counterpart; derived data): sv32_out[d][32] and the per-lane
+ * Gray-code table tlane_out[d][32][2] used by the warp decomposition of the skip-ahead. */
+int orp_sobol_pack(int d, int bits, const uint32_t* sv, const uint32_t* shift, uint32_t* sv32_out, uint32_t* tlane_out);
+
+/* ---------------------------------------------------------------- a-2  Sobol points (device) */
+
+/* Replaces qmc.Sobol.random_base2 / random / fast_forward -> _draw (scipy/stats/_qmc.py:1862-1917,
+ * 1932-1957 <- Replicating_Portfolio.py:56): integer points x_i, i in [start, start+count), for all d
+ * dimensions; u = x * 2^-30.  layout 0: d_out[count][d] (SciPy's), layout 1: d_out[d][count]. */
+int orp_sobol_points(const uint32_t* d_sv32, const uint32_t* d_tlane, int d, uint64_t start, uint64_t count,
+                     int layout, uint32_t* d_out, void* stream);
+
+/* a-3: scipy.stats.norm.ppf -> scipy.special.ndtri (Replicating_Portfolio.py:57) on integer points:
+ * d_z[i] = ndtri(d_x[i] * 2^-30), ndtri(0) = -inf.  Test/inspection entry; the path kernels inline it. */
+int orp_ndtri_u32(const uint32_t* d_x, uint64_t n, double* d_z, void* stream);
+
+/* ---------------------------------------------------------------- a-4/5/8  paths (device) */
+
+enum { ORP_MODEL_GBM_LOG = 0, ORP_MODEL_GBM_ARITH = 1, ORP_MODEL_SV = 2 };
+enum { ORP_ORDER_INCREMENTAL = 0, ORP_ORDER_BRIDGE = 1 };
+enum { ORP_F64 = 0, ORP_F32 = 1 };
+
+typedef struct orp_path_params {
+    int32_t model;       /* ORP_MODEL_* */
+    int32_t ordering;    /* ORP_ORDER_* */
+    int32_t n_steps;     /* D; the engines have d = D + 1 dimensions, step t uses dimension t, dimension 0 unused */
+    int32_t keep_every;  /* the reference's `reduction` (Replicating_Portfolio.py:92-93): column t is stored iff t % keep_every == 0 */
+    int32_t out_dtype;   /* ORP_F64 / ORP_F32 (arithmetic is fp64 either way) */
+    int32_t reserved;
+    double s0;           /* Y / S0 */
+    double mu;           /* drift: mu (Replicating_Portfolio.py:65, :287) or r (European Options.ipynb cell 6) */
+    double sigma;        /* GBM volatility */
+    double dt;           /* fine-grid step */
+    double v0, a, b, c;  /* stochastic volatility: s0, a, b, c of Replicating_Portfolio.py:244-249, 285 */
+} orp_path_params;
+
+/* Replaces sobol_norm + the Euler loops + np.exp + the column slice:
+ *   GBM_ARITH  Replicating_Portfolio.py:60-65, 93
+ *   GBM_LOG    European Options.ipynb cell 6 (raw 156-165) and cell 7 (raw 205-207)
+ *   SV         Replicating_Portfolio.py:274-289, 93   (second engine d_sv32_b/d_tlane_b drives the volatility)
+ * Output is TIME-MAJOR: d_out[col * ld + (i - start)], col = t / keep_every, 0 <= col <= D / keep_every, ld >= count.
+ * d_bridge: device schedule from orp_bridge_schedule (ordering = BRIDGE) or NULL. */
+int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const uint32_t* d_tlane,
+              const uint32_t* d_sv32_b, const uint32_t* d_tlane_b, const void* d_bridge,
+              uint64_t start, uint64_t count, void* d_out, uint64_t ld, void* stream);
+
+/* Brownian-bridge schedule for D steps (NEW feature, no reference counterpart; specification in
+ * oracle/bridge.py).  Host function: fills sched_out (orp_bridge_schedule_bytes(D) bytes) which the caller
+ * copies to the device. */
+uint64_t orp_bridge_schedule_bytes(int n_steps);
+int orp_bridge_schedule(int n_steps, void* sched_out);
+
+/* ---------------------------------------------------------------- a-6/7  payoff + reductions (device) */
+
+enum { ORP_PAYOFF_CALL = 0, ORP_PAYOFF_PUT = 1, ORP_PAYOFF_FLOOR = 2 };
+#define ORP_MAX_OPTIONS 64
+
+/* Replaces the payoff and summary block: CALL/PUT European Options.ipynb cell 8 (raw 328-329, 344, 347),
+ * FLOOR Replicating_Portfolio.py:88-89, means :185.  For option j: sum_i payoff(S[cols[j]][i], strikes[j])
+ * and the out-of-the-money count (CALL/PUT: payoff <= 0; FLOOR: S < s0).
+ * d_paths time-major [*][ld], dtype as written by orp_paths.  d_sums[n_opt], d_otm[n_opt] (fp64).
+ * d_values_out (optional, fp32 [count]): payoff of option 0 times value_scale — values[:, -1] of
+ * Replicating_Portfolio.py:184 / European Options.ipynb cell 13.
+ * d_scratch: orp_payoff_scratch_bytes(n_opt) bytes of device scratch (per-block partial sums; the two-stage
+ * fixed-order reduction makes the result independent of scheduling). */
+uint64_t orp_payoff_scratch_bytes(int n_opt);
+int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, uint64_t count, int kind, int n_opt,
+                      const double* strikes, const int32_t* cols, double s0, double value_scale,
+                      float* d_values_out, double* d_sums, double* d_otm, void* d_scratch, void* stream);
+
+/* ---------------------------------------------------------------- a-9/10/11  replicating-portfolio fit (device) */
+
+enum { ORP_NET_EO = 0, ORP_NET_RP = 1 };       /* 1->8->8->1 (psi = 1 - phi), 97 params; 3->8->8->2, 122 params */
+enum { ORP_LOSS_MSE = 0, ORP_LOSS_PINBALL = 1 }; /* 'mse'; quantile_loss q = .99 (Replicating_Portfolio.py:138-142) */
+#define ORP_FIT_MAX_PARAMS 128
+#define ORP_FIT_STATE_DOUBLES 1024
+
+int orp_fit_n_params(int net);
+
+/* One time step of the backward loop (Replicating_Portfolio.py:195-201; European Options.ipynb cell 13 raw 3551-3558).
+ * Feature/price columns are read in place from the time-major path array and cast to fp32 as Keras does. */
+typedef struct orp_fit_batch {
+    int32_t net;            /* ORP_NET_* */
+    int32_t loss;           /* ORP_LOSS_* */
+    int32_t paths_dtype;    /* dtype of d_s_t / d_s_t1 */
+    int32_t reserved;
+    uint64_t count;         /* local paths */
+    const void* d_s_t;      /* S column t   (feature, and price for the roll-back) */
+    const void* d_s_t1;     /* S column t+1 (price the fit is scored on) */
+    const float* d_feat1;   /* RP net only: N_t / N per path, or NULL (= 1) */
+    const float* d_feat2;   /* RP net only: lambda_t per path, or NULL (= 0) */
+    const float* d_target;  /* values[:, t+1] */
+    double inv_scale;       /* 1 / ADJUSTMENT_FACTOR applied to prices (EO: 1/S0; RP: 1) */
+    double bond_t, bond_t1; /* B_t, B_{t+1} (Replicating_Portfolio.py:68) */
+} orp_fit_batch;
+
+uint64_t orp_fit_scratch_bytes(void);
+
+/* Scaled mode, stage 1 of one epoch: fused forward + backward over all local paths; writes the fixed-order
+ * reduced vector d_gsum[ORP_FIT_MAX_PARAMS + 2] = (sum of per-sample gradients, sum of per-sample losses, count)
+ * in fp64.  Multi-GPU: the caller all-reduces d_gsum (NCCL, sum) between stage 1 and stage 2.
+ * No-op when the control block says the fit has stopped.  Replaces the inside of keras Model.fit
+ * (Replicating_Portfolio.py:211) for one optimiser step. */
+int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const double* d_state, double* d_gsum,
+                 void* d_scratch, void* stream);
+
+/* Stage 2: Adam step (Keras formula, eps 1e-7), epoch loss, LearningRateScheduler (Replicating_Portfolio.py:128-136)
+ * and EarlyStopping(monitor='loss', restore_best_weights=True) bookkeeping (:174, :206), all on the device so the
+ * host can enqueue epochs without synchronising.  d_state: ORP_FIT_STATE_DOUBLES doubles, layout in orp_fit.cu. */
+int orp_fit_update(int net, float* d_params, double* d_state, const double* d_gsum, void* stream);
+
+/* Starts a Model.fit call: resets the early-stopping state, keeps weights and Adam moments (they persist across
+ * time steps, Replicating_Portfolio.py:203-211).  use_schedule = 1 for the first fit. */
+int orp_fit_begin(double* d_state, int epochs, int patience, int use_schedule, void* stream);
+/* Initialises weights-independent optimiser state (Adam moments, step, lr = 1e-3). */
+int orp_fit_init(double* d_state, void* stream);
+/* Ends a fit: restores the best weights when the stop fired early (TF 2.x semantics). */
+int orp_fit_end(int net, float* d_params, double* d_state, void* stream);
+
+/* Replaces model.predict(X0) / get_phi_psi_VaR means (Replicating_Portfolio.py:212, 103-115, 229-235):
+ * d_values_out[i] = phi_i * S_t * inv_scale + psi_i * B_t * inv_scale (fp32), and
+ * d_sums[4] = (sum V, sum phi, sum psi, sum |target - V(prices at t+1)|). */
+int orp_fit_predict(const orp_fit_batch* b, const float* d_params, float* d_values_out, double* d_sums,
+                    void* d_scratch, void* stream);
+
+/* Keras-faithful mode: ONE epoch of mini-batch training (batch_size samples per Adam step, visiting samples in
+ * the order perm(epoch_seed)), serial by construction, run by a single thread block.  Replaces Model.fit's inner
+ * loop with batch_size=512, shuffle=True (Replicating_Portfolio.py:211). */
+int orp_fit_epoch_minibatch(const orp_fit_batch* b, float* d_params, double* d_state, int batch_size,
+                            uint64_t epoch_seed, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORP_B200_H */

@@ -1,0 +1,436 @@
+// Sobol points, inverse normal and the fused path kernels (SURVEY.md §8 rows a-2 .. a-5, a-8).
+//
+// One persistent thread block per SM keeps the 116 KB inverse-normal coefficient table in shared
+// memory; a warp owns 64 consecutive Sobol indices (two per lane) and walks the time axis with the
+// whole path state in registers, storing the kept columns time-major (256 contiguous bytes per warp
+// store).  Nothing but the kept columns ever touches HBM: 8 B (fp64) or 4 B (fp32) per stored path-step.
+#include "orp_common.h"
+#include "orp_device.cuh"
+
+#include <utility>
+#include <vector>
+
+namespace orp {
+
+constexpr int kPathThreads = 1024;   // 32 warps: 2048 paths per block tile
+constexpr int kWarpPaths = 64;
+
+// ------------------------------------------------------------------------------------------------
+// a-3 test entry: z[i] = ndtri(x[i] * 2^-30)
+__global__ void __launch_bounds__(256) ndtri_u32_kernel(const uint32_t* __restrict__ x, uint64_t n,
+                                                        double* __restrict__ z) {
+    extern __shared__ __align__(128) char s_tab[];
+    load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
+    __syncthreads();
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+        z[i] = ndtri_bits(x[i], s_tab);
+}
+
+// ------------------------------------------------------------------------------------------------
+// a-2: integer points.  layout 1: out[t][count] (native), layout 0: out[count][d] (SciPy's) through a
+// per-warp shared-memory transpose so both are written with full 128-byte lines.
+constexpr int kPointsWarps = 4;
+
+template <int LAYOUT>
+__global__ void __launch_bounds__(kPointsWarps * 32)
+sobol_points_kernel(const uint32_t* __restrict__ sv32, const uint2* __restrict__ tlane, int d, uint64_t start,
+                    uint64_t count, uint32_t* __restrict__ out) {
+    __shared__ uint32_t s_tile[LAYOUT == 0 ? kPointsWarps : 1][64][33];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t end = start + count;
+    const uint64_t w_first = start / kWarpPaths, w_last = (end - 1) / kWarpPaths;
+    const uint64_t n_tiles = w_last - w_first + 1;
+    for (uint64_t tile = (uint64_t)blockIdx.x * kPointsWarps + warp; tile < n_tiles;
+         tile += (uint64_t)gridDim.x * kPointsWarps) {
+        const uint64_t w = w_first + tile;
+        const uint64_t i0 = w * kWarpPaths + lane, i1 = i0 + 32;
+        const bool ok0 = i0 >= start && i0 < end, ok1 = i1 >= start && i1 < end;
+        for (int t0 = 0; t0 < d; t0 += 32) {
+            const int my_dim = t0 + lane;
+            const uint32_t bl = my_dim < d ? warp_base(sv32, my_dim, w) : 0u;
+            const int nc = min(32, d - t0);
+            for (int s = 0; s < nc; ++s) {
+                const int t = t0 + s;
+                const uint32_t base = __shfl_sync(kFull, bl, s);
+                const uint2 tl = __ldg(tlane + (size_t)t * 32 + lane);
+                const uint32_t x0 = base ^ tl.x, x1 = base ^ tl.y;
+                if (LAYOUT == 1) {
+                    if (ok0) out[(size_t)t * count + (i0 - start)] = x0;
+                    if (ok1) out[(size_t)t * count + (i1 - start)] = x1;
+                } else {
+                    s_tile[warp][lane][s] = x0;
+                    s_tile[warp][lane + 32][s] = x1;
+                }
+            }
+            if (LAYOUT == 0) {
+                __syncwarp();
+                for (int r = 0; r < 64; ++r) {
+                    const uint64_t i = w * kWarpPaths + r;
+                    if (i >= start && i < end && lane < nc)
+                        out[(size_t)(i - start) * d + t0 + lane] = s_tile[warp][r][lane];
+                }
+                __syncwarp();
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// a-4 / a-5 / a-8: fused Sobol -> ndtri -> step -> store-kept-columns.
+
+struct PathArgs {
+    const uint32_t* sv32_a;
+    const uint2* tlane_a;
+    const uint32_t* sv32_b;   // SV only: the volatility engine (seed 1234 in the reference)
+    const uint2* tlane_b;
+    void* out;
+    uint64_t ld, start, count;
+    int n_steps, keep_every;
+    double s0;                // Y / S0
+    double c_drift;           // GBM_LOG: (mu - sigma^2/2) dt;  GBM_ARITH: mu dt;  SV: mu
+    double c_vol;             // GBM: sigma sqrt(dt);           SV: sqrt(dt)
+    double dt, v0, a, b, c;
+};
+
+template <typename OutT>
+__device__ __forceinline__ void store_col(void* out, uint64_t ld, int col, uint64_t j, double v) {
+    reinterpret_cast<OutT*>(out)[(size_t)col * ld + j] = (OutT)v;
+}
+
+// One time step for the two paths of a lane.  z: normals of the price engine, y: of the volatility engine.
+template <int MODEL>
+__device__ __forceinline__ void advance(const PathArgs& a, double& s_0, double& s_1, double& v_0, double& v_1,
+                                        double z0, double z1, double y0, double y1) {
+    if (MODEL == ORP_MODEL_GBM_LOG) {
+        // lnS_t = lnS_{t-1} + ((r - sigma^2/2) dt + sigma sqrt(dt) W_t)                      EO cell 6
+        s_0 += fma(a.c_vol, z0, a.c_drift);
+        s_1 += fma(a.c_vol, z1, a.c_drift);
+    } else if (MODEL == ORP_MODEL_GBM_ARITH) {
+        // Y_t = Y_{t-1} + Y_{t-1} (mu dt + sigma sqrt(dt) W_t)                                RP.py:65
+        s_0 = fma(s_0, fma(a.c_vol, z0, a.c_drift), s_0);
+        s_1 = fma(s_1, fma(a.c_vol, z1, a.c_drift), s_1);
+    } else {
+        // v_t = v + a (b - v) + c sqrt(v dt) Wv_t;  lnY_t = lnY + ((mu - v_t^2/2) dt + v_t sqrt(dt) W_t)   RP.py:285-287
+        v_0 = (v_0 + a.a * (a.b - v_0)) + (a.c * sqrt(v_0 * a.dt)) * y0;
+        v_1 = (v_1 + a.a * (a.b - v_1)) + (a.c * sqrt(v_1 * a.dt)) * y1;
+        s_0 += (a.c_drift - 0.5 * (v_0 * v_0)) * a.dt + (v_0 * a.c_vol) * z0;
+        s_1 += (a.c_drift - 0.5 * (v_1 * v_1)) * a.dt + (v_1 * a.c_vol) * z1;
+    }
+}
+
+template <int MODEL, typename OutT>
+__global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a) {
+    extern __shared__ __align__(128) char s_tab[];
+    load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int kWarps = kPathThreads / 32;
+    const uint64_t end = a.start + a.count;
+    const uint64_t w_first = a.start / kWarpPaths, w_last = (end - 1) / kWarpPaths;
+    const uint64_t n_tiles = w_last - w_first + 1;
+    const int D = a.n_steps;
+
+    // block-contiguous tiling: the 32 warps of a block work on 2048 consecutive paths
+    for (uint64_t tile = (uint64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (uint64_t)gridDim.x * kWarps) {
+        const uint64_t w = w_first + tile;
+        const uint64_t i0 = w * kWarpPaths + lane, i1 = i0 + 32;
+        const bool ok0 = i0 >= a.start && i0 < end, ok1 = i1 >= a.start && i1 < end;
+        const uint64_t j0 = i0 - a.start, j1 = i1 - a.start;
+
+        // state: GBM_LOG ln S; GBM_ARITH S; SV ln Y and v
+        double s_0, s_1, v_0 = a.v0, v_1 = a.v0;
+        if (MODEL == ORP_MODEL_GBM_ARITH) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
+        if (ok0) store_col<OutT>(a.out, a.ld, 0, j0, a.s0);
+        if (ok1) store_col<OutT>(a.out, a.ld, 0, j1, a.s0);
+        int next_keep = a.keep_every, col = 1;
+
+        for (int t0 = 1; t0 <= D; t0 += 32) {
+            const int my_dim = t0 + lane;
+            uint32_t bl_a = 0u, bl_b = 0u;
+            if (my_dim <= D) {
+                bl_a = warp_base(a.sv32_a, my_dim, w);
+                if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, my_dim, w);
+            }
+            const int nc = min(32, D - t0 + 1);
+            for (int s = 0; s < nc; ++s) {
+                const int t = t0 + s;
+                const uint32_t base = __shfl_sync(kFull, bl_a, s);
+                const uint2 tl = __ldg(a.tlane_a + (size_t)t * 32 + lane);
+                const double z0 = ndtri_bits(base ^ tl.x, s_tab);
+                const double z1 = ndtri_bits(base ^ tl.y, s_tab);
+                double y0 = 0.0, y1 = 0.0;
+                if (MODEL == ORP_MODEL_SV) {
+                    const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
+                    const uint2 tb = __ldg(a.tlane_b + (size_t)t * 32 + lane);
+                    y0 = ndtri_bits(base_b ^ tb.x, s_tab);
+                    y1 = ndtri_bits(base_b ^ tb.y, s_tab);
+                }
+                advance<MODEL>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
+                if (t == next_keep) {
+                    double o0 = s_0, o1 = s_1;
+                    if (MODEL != ORP_MODEL_GBM_ARITH) { o0 = exp(s_0); o1 = exp(s_1); }
+                    if (ok0) store_col<OutT>(a.out, a.ld, col, j0, o0);
+                    if (ok1) store_col<OutT>(a.out, a.ld, col, j1, o1);
+                    next_keep += a.keep_every;
+                    ++col;
+                }
+            }
+        }
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// Brownian-bridge ordering (NEW feature; specification in oracle/bridge.py, no reference counterpart).
+// Sobol coordinates are random-access in the DIMENSION as well as in the index, so the bridge needs no
+// buffering of a path's D normals: the bisection tree is walked depth-first in time order with a stack
+// of at most ceil(log2 D) + 1 pending right end-points per path.  The walk is the same for every path,
+// so the host compiles it into a program of D ops (orp_bridge_schedule): op o builds one node from
+// Sobol dimension ops[o].dim and is followed by ops[o].emits emissions (pop + time step).
+struct BridgeOp { int32_t dim; int32_t emits; double wl, wr, sd; };
+constexpr int kBridgeMaxDepth = 20;
+
+template <int MODEL, typename OutT>
+__global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const PathArgs a, const BridgeOp* __restrict__ ops) {
+    extern __shared__ __align__(128) char s_tab[];
+    load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int kWarps = kPathThreads / 32;
+    constexpr int NS = MODEL == ORP_MODEL_SV ? 4 : 2;      // stacks: price (2 paths) [+ volatility (2 paths)]
+    const uint64_t end = a.start + a.count;
+    const uint64_t w_first = a.start / kWarpPaths, w_last = (end - 1) / kWarpPaths;
+    const uint64_t n_tiles = w_last - w_first + 1;
+    const int D = a.n_steps;
+
+    for (uint64_t tile = (uint64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (uint64_t)gridDim.x * kWarps) {
+        const uint64_t w = w_first + tile;
+        const uint64_t i0 = w * kWarpPaths + lane, i1 = i0 + 32;
+        const bool ok0 = i0 >= a.start && i0 < end, ok1 = i1 >= a.start && i1 < end;
+        const uint64_t j0 = i0 - a.start, j1 = i1 - a.start;
+
+        double s_0, s_1, v_0 = a.v0, v_1 = a.v0;
+        if (MODEL == ORP_MODEL_GBM_ARITH) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
+        if (ok0) store_col<OutT>(a.out, a.ld, 0, j0, a.s0);
+        if (ok1) store_col<OutT>(a.out, a.ld, 0, j1, a.s0);
+        int next_keep = a.keep_every, col = 1, t = 0, sp = -1;
+        double stk[NS][kBridgeMaxDepth];
+        double cur[NS];
+#pragma unroll
+        for (int q = 0; q < NS; ++q) cur[q] = 0.0;           // W(0) = 0
+
+        for (int o0 = 0; o0 < D; o0 += 32) {
+            uint32_t bl_a = 0u, bl_b = 0u;
+            if (o0 + lane < D) {
+                const int my_dim = ops[o0 + lane].dim;
+                bl_a = warp_base(a.sv32_a, my_dim, w);
+                if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, my_dim, w);
+            }
+            const int nc = min(32, D - o0);
+            for (int s = 0; s < nc; ++s) {
+                const BridgeOp op = ops[o0 + s];
+                double zz[NS];
+                {
+                    const uint32_t base = __shfl_sync(kFull, bl_a, s);
+                    const uint2 tl = __ldg(a.tlane_a + (size_t)op.dim * 32 + lane);
+                    zz[0] = ndtri_bits(base ^ tl.x, s_tab);
+                    zz[1] = ndtri_bits(base ^ tl.y, s_tab);
+                }
+                if (MODEL == ORP_MODEL_SV) {
+                    const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
+                    const uint2 tb = __ldg(a.tlane_b + (size_t)op.dim * 32 + lane);
+                    zz[NS - 2] = ndtri_bits(base_b ^ tb.x, s_tab);
+                    zz[NS - 1] = ndtri_bits(base_b ^ tb.y, s_tab);
+                }
+                // W_m = wl W_left + wr W_right + sd z   (left = last emitted node, right = stack top)
+#pragma unroll
+                for (int q = 0; q < NS; ++q) {
+                    const double right = sp >= 0 ? stk[q][sp] : 0.0;
+                    stk[q][sp + 1] = op.wl * cur[q] + op.wr * right + op.sd * zz[q];
+                }
+                ++sp;
+                for (int e = 0; e < op.emits; ++e) {
+                    double inc[NS];
+#pragma unroll
+                    for (int q = 0; q < NS; ++q) { const double wj = stk[q][sp]; inc[q] = wj - cur[q]; cur[q] = wj; }
+                    --sp;
+                    ++t;
+                    advance<MODEL>(a, s_0, s_1, v_0, v_1, inc[0], inc[1], inc[NS - 2], inc[NS - 1]);
+                    if (t == next_keep) {
+                        double q0 = s_0, q1 = s_1;
+                        if (MODEL != ORP_MODEL_GBM_ARITH) { q0 = exp(s_0); q1 = exp(s_1); }
+                        if (ok0) store_col<OutT>(a.out, a.ld, col, j0, q0);
+                        if (ok1) store_col<OutT>(a.out, a.ld, col, j1, q1);
+                        next_keep += a.keep_every;
+                        ++col;
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <typename K>
+static int set_table_smem(K kernel) {
+    static bool done[64] = {false};
+    int dev = 0;
+    ORP_CUDA(cudaGetDevice(&dev));
+    (void)done;
+    ORP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNdtriTableBytes));
+    return ORP_OK;
+}
+
+template <int MODEL, typename OutT>
+static int launch_paths(const PathArgs& a, cudaStream_t st) {
+    int rc = set_table_smem(paths_kernel<MODEL, OutT>);
+    if (rc) return rc;
+    const uint64_t n_tiles = (a.start + a.count - 1) / kWarpPaths - a.start / kWarpPaths + 1;
+    const uint64_t want = (n_tiles + 31) / 32;
+    const int grid = (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
+    paths_kernel<MODEL, OutT><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a);
+    ORP_LAUNCH_CHECK("paths_kernel");
+    return ORP_OK;
+}
+
+
+template <int MODEL, typename OutT>
+static int launch_paths_bridge(const PathArgs& a, const void* d_bridge, cudaStream_t st) {
+    int rc = set_table_smem(paths_bridge_kernel<MODEL, OutT>);
+    if (rc) return rc;
+    const uint64_t n_tiles = (a.start + a.count - 1) / kWarpPaths - a.start / kWarpPaths + 1;
+    const uint64_t want = (n_tiles + 31) / 32;
+    const int grid = (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
+    paths_bridge_kernel<MODEL, OutT><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a, reinterpret_cast<const BridgeOp*>(d_bridge));
+    ORP_LAUNCH_CHECK("paths_bridge_kernel");
+    return ORP_OK;
+}
+
+}  // namespace orp
+
+using namespace orp;
+
+extern "C" uint64_t orp_bridge_schedule_bytes(int n_steps) { return n_steps > 0 ? (uint64_t)n_steps * sizeof(BridgeOp) : 0; }
+
+// Breadth-first bisection numbers the nodes (Sobol dimension k drives the k-th node built); the ops are
+// then emitted in depth-first time order.  Same tree, same weights as oracle/bridge.py::bridge_schedule.
+extern "C" int orp_bridge_schedule(int n_steps, void* sched_out) {
+    ORP_REQUIRE(sched_out, "null pointer");
+    ORP_REQUIRE(n_steps >= 1 && n_steps + 1 <= ORP_SOBOL_MAXDIM, "n_steps must be in [1, %d]", ORP_SOBOL_MAXDIM - 1);
+    const int D = n_steps;
+    std::vector<int> dim_of(D + 1, 0);
+    {
+        std::vector<std::pair<int, int>> q;
+        q.reserve(2 * (size_t)D + 2);
+        dim_of[D] = 1;
+        int next_dim = 2;
+        q.emplace_back(0, D);
+        for (size_t h = 0; h < q.size(); ++h) {
+            const int l = q[h].first, r = q[h].second;
+            if (r - l >= 2) {
+                const int m = (l + r) / 2;
+                dim_of[m] = next_dim++;
+                q.emplace_back(l, m);
+                q.emplace_back(m, r);
+            }
+        }
+    }
+    BridgeOp* ops = reinterpret_cast<BridgeOp*>(sched_out);
+    int n_ops = 0, depth_max = 0;
+    std::vector<int> stack;                      // node indices, top = nearest pending right end-point
+    ops[n_ops++] = BridgeOp{dim_of[D], 0, 0.0, 0.0, sqrt((double)D)};
+    stack.push_back(D);
+    int left = 0;
+    for (int j = 1; j <= D; ++j) {
+        while (stack.back() > j) {
+            const int r = stack.back(), m = (left + r) / 2;
+            ops[n_ops++] = BridgeOp{dim_of[m], 0, (double)(r - m) / (double)(r - left), (double)(m - left) / (double)(r - left),
+                                    sqrt((double)(m - left) * (double)(r - m) / (double)(r - left))};
+            stack.push_back(m);
+            if ((int)stack.size() > depth_max) depth_max = (int)stack.size();
+        }
+        ops[n_ops - 1].emits += 1;               // emission of node j follows the last op executed so far
+        stack.pop_back();
+        left = j;
+    }
+    ORP_REQUIRE(n_ops == D && depth_max < kBridgeMaxDepth, "bridge schedule inconsistent (ops %d, depth %d)", n_ops, depth_max);
+    return ORP_OK;
+}
+
+extern "C" int orp_ndtri_u32(const uint32_t* d_x, uint64_t n, double* d_z, void* stream) {
+    ORP_REQUIRE(d_x && d_z, "null pointer");
+    if (n == 0) return ORP_OK;
+    int rc = set_table_smem(ndtri_u32_kernel);
+    if (rc) return rc;
+    const uint64_t blocks = (n + 255) / 256;
+    const int grid = (int)(blocks < (uint64_t)sm_count() ? blocks : (uint64_t)sm_count());
+    ndtri_u32_kernel<<<grid, 256, kNdtriTableBytes, (cudaStream_t)stream>>>(d_x, n, d_z);
+    ORP_LAUNCH_CHECK("ndtri_u32_kernel");
+    return ORP_OK;
+}
+
+extern "C" int orp_sobol_points(const uint32_t* d_sv32, const uint32_t* d_tlane, int d, uint64_t start, uint64_t count,
+                                int layout, uint32_t* d_out, void* stream) {
+    ORP_REQUIRE(d_sv32 && d_tlane && (d_out || count == 0), "null pointer");
+    ORP_REQUIRE(d >= 1 && d <= ORP_SOBOL_MAXDIM, "Maximum supported dimensionality is %d.", ORP_SOBOL_MAXDIM);
+    ORP_REQUIRE(layout == 0 || layout == 1, "layout must be 0 (points-major) or 1 (dimension-major)");
+    ORP_REQUIRE(start + count <= (1ull << ORP_SOBOL_BITS), "At most 2**%d=%llu distinct points can be generated.",
+                ORP_SOBOL_BITS, 1ull << ORP_SOBOL_BITS);
+    if (count == 0) return ORP_OK;
+    const uint64_t n_tiles = (start + count - 1) / kWarpPaths - start / kWarpPaths + 1;
+    const uint64_t want = (n_tiles + kPointsWarps - 1) / kPointsWarps;
+    const uint64_t cap = (uint64_t)sm_count() * 8;
+    const int grid = (int)(want < cap ? want : cap);
+    const uint2* tl = reinterpret_cast<const uint2*>(d_tlane);
+    if (layout == 0)
+        sobol_points_kernel<0><<<grid, kPointsWarps * 32, 0, (cudaStream_t)stream>>>(d_sv32, tl, d, start, count, d_out);
+    else
+        sobol_points_kernel<1><<<grid, kPointsWarps * 32, 0, (cudaStream_t)stream>>>(d_sv32, tl, d, start, count, d_out);
+    ORP_LAUNCH_CHECK("sobol_points_kernel");
+    return ORP_OK;
+}
+
+extern "C" int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const uint32_t* d_tlane,
+                         const uint32_t* d_sv32_b, const uint32_t* d_tlane_b, const void* d_bridge, uint64_t start,
+                         uint64_t count, void* d_out, uint64_t ld, void* stream) {
+    ORP_REQUIRE(p && d_sv32 && d_tlane && (d_out || count == 0), "null pointer");
+    ORP_REQUIRE(p->n_steps >= 1 && p->n_steps + 1 <= ORP_SOBOL_MAXDIM, "n_steps must be in [1, %d]", ORP_SOBOL_MAXDIM - 1);
+    ORP_REQUIRE(p->keep_every >= 1, "keep_every must be >= 1");
+    ORP_REQUIRE(start + count <= (1ull << ORP_SOBOL_BITS), "At most 2**%d=%llu distinct points can be generated.",
+                ORP_SOBOL_BITS, 1ull << ORP_SOBOL_BITS);
+    ORP_REQUIRE(ld >= count, "ld (%llu) must be >= count (%llu)", (unsigned long long)ld, (unsigned long long)count);
+    ORP_REQUIRE(p->out_dtype == ORP_F64 || p->out_dtype == ORP_F32, "out_dtype must be ORP_F64 or ORP_F32");
+    ORP_REQUIRE(p->model != ORP_MODEL_SV || (d_sv32_b && d_tlane_b), "the SV model needs a second Sobol engine");
+    ORP_REQUIRE(p->ordering == ORP_ORDER_INCREMENTAL || (p->ordering == ORP_ORDER_BRIDGE && d_bridge),
+                "ordering must be ORP_ORDER_INCREMENTAL, or ORP_ORDER_BRIDGE with a schedule");
+    if (count == 0) return ORP_OK;
+
+    PathArgs a;
+    a.sv32_a = d_sv32;  a.tlane_a = reinterpret_cast<const uint2*>(d_tlane);
+    a.sv32_b = d_sv32_b; a.tlane_b = reinterpret_cast<const uint2*>(d_tlane_b);
+    a.out = d_out; a.ld = ld; a.start = start; a.count = count;
+    a.n_steps = p->n_steps; a.keep_every = p->keep_every;
+    a.s0 = p->s0; a.dt = p->dt; a.v0 = p->v0; a.a = p->a; a.b = p->b; a.c = p->c;
+    const double sqdt = sqrt(p->dt);
+    switch (p->model) {
+        case ORP_MODEL_GBM_LOG:   a.c_drift = (p->mu - 0.5 * p->sigma * p->sigma) * p->dt; a.c_vol = p->sigma * sqdt; break;
+        case ORP_MODEL_GBM_ARITH: a.c_drift = p->mu * p->dt;                              a.c_vol = p->sigma * sqdt; break;
+        case ORP_MODEL_SV:        a.c_drift = p->mu;                                      a.c_vol = sqdt;            break;
+        default: return fail(ORP_E_VALUE, "unknown model %d", p->model);
+    }
+    if (p->ordering == ORP_ORDER_BRIDGE) {
+        switch (p->model) {
+            case ORP_MODEL_GBM_LOG:   return p->out_dtype == ORP_F32 ? launch_paths_bridge<ORP_MODEL_GBM_LOG, float>(a, d_bridge, (cudaStream_t)stream)   : launch_paths_bridge<ORP_MODEL_GBM_LOG, double>(a, d_bridge, (cudaStream_t)stream);
+            case ORP_MODEL_GBM_ARITH: return p->out_dtype == ORP_F32 ? launch_paths_bridge<ORP_MODEL_GBM_ARITH, float>(a, d_bridge, (cudaStream_t)stream) : launch_paths_bridge<ORP_MODEL_GBM_ARITH, double>(a, d_bridge, (cudaStream_t)stream);
+            default:                  return p->out_dtype == ORP_F32 ? launch_paths_bridge<ORP_MODEL_SV, float>(a, d_bridge, (cudaStream_t)stream)        : launch_paths_bridge<ORP_MODEL_SV, double>(a, d_bridge, (cudaStream_t)stream);
+        }
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool f32 = p->out_dtype == ORP_F32;
+    switch (p->model) {
+        case ORP_MODEL_GBM_LOG:   return f32 ? launch_paths<ORP_MODEL_GBM_LOG, float>(a, st)   : launch_paths<ORP_MODEL_GBM_LOG, double>(a, st);
+        case ORP_MODEL_GBM_ARITH: return f32 ? launch_paths<ORP_MODEL_GBM_ARITH, float>(a, st) : launch_paths<ORP_MODEL_GBM_ARITH, double>(a, st);
+        default:                  return f32 ? launch_paths<ORP_MODEL_SV, float>(a, st)        : launch_paths<ORP_MODEL_SV, double>(a, st);
+    }
+}

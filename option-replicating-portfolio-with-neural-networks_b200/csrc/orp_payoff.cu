@@ -1,0 +1,136 @@
+// Terminal payoff and summary reductions.
+//
+// HBM-bound: one read of each maturity column (8 B or 4 B per path), optional 4 B write of the
+// terminal value.  Per-option sums are reduced warp-shuffle -> shared memory -> one fp64 partial per
+// block in scratch -> a second, single-block pass that adds the partials in block order, so the
+// result does not depend on scheduling (and matches on every launch bit for bit).
+#include "orp_common.h"
+
+namespace orp {
+
+constexpr int kPayThreads = 256;
+constexpr int kPayChunk = 8;          // options handled together (shared column loads hit L1)
+
+struct PayoffArgs {
+    const void* paths;
+    uint64_t ld, count;
+    int kind, n_opt;
+    double s0, value_scale;
+    float* values_out;
+    double* partials;                 // [gridDim.y][gridDim.x][2 * kPayChunk]
+    double strikes[ORP_MAX_OPTIONS];
+    int32_t cols[ORP_MAX_OPTIONS];
+};
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kPayThreads) payoff_partial_kernel(const PayoffArgs a) {
+    const int chunk = blockIdx.y;
+    const int o_first = chunk * kPayChunk;
+    const int n_here = min(kPayChunk, a.n_opt - o_first);
+    const T* __restrict__ paths = reinterpret_cast<const T*>(a.paths);
+
+    double sum[kPayChunk], otm[kPayChunk];
+#pragma unroll
+    for (int k = 0; k < kPayChunk; ++k) sum[k] = otm[k] = 0.0;
+
+    for (uint64_t i = (uint64_t)blockIdx.x * kPayThreads + threadIdx.x; i < a.count; i += (uint64_t)gridDim.x * kPayThreads) {
+        int last_col = -1;
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < kPayChunk; ++k) {
+            if (k < n_here) {
+                const int col = a.cols[o_first + k];
+                if (col != last_col) { s = (double)paths[(size_t)col * a.ld + i]; last_col = col; }
+                const double K = a.strikes[o_first + k];
+                double pay, is_otm;
+                if (a.kind == ORP_PAYOFF_CALL)      { pay = fmax(s - K, 0.0); is_otm = pay > 0.0 ? 0.0 : 1.0; }   // EO cell 8
+                else if (a.kind == ORP_PAYOFF_PUT)  { pay = fmax(K - s, 0.0); is_otm = pay > 0.0 ? 0.0 : 1.0; }
+                else                                { pay = s > K ? s : K;    is_otm = s < a.s0 ? 1.0 : 0.0; }    // RP.py:88-89
+                // np.maximum propagates NaN, fmax does not
+                if (a.kind != ORP_PAYOFF_FLOOR && s != s) pay = s;
+                sum[k] += pay;
+                otm[k] += is_otm;
+                if (k == 0 && chunk == 0 && a.values_out) a.values_out[i] = (float)(pay * a.value_scale);
+            }
+        }
+    }
+
+    __shared__ double s_red[kPayThreads / 32][2 * kPayChunk];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < kPayChunk; ++k) {
+        const double a_ = warp_sum(sum[k]), b_ = warp_sum(otm[k]);
+        if (lane == 0) { s_red[warp][2 * k] = a_; s_red[warp][2 * k + 1] = b_; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2 * kPayChunk) {
+        double t = 0.0;
+        for (int w = 0; w < kPayThreads / 32; ++w) t += s_red[w][threadIdx.x];
+        a.partials[((size_t)chunk * gridDim.x + blockIdx.x) * (2 * kPayChunk) + threadIdx.x] = t;
+    }
+}
+
+__global__ void payoff_final_kernel(const double* __restrict__ partials, int n_blocks, int n_opt,
+                                    double* __restrict__ sums, double* __restrict__ otm) {
+    const int o = blockIdx.x * blockDim.x + threadIdx.x;       // one thread per (option, quantity)
+    if (o >= 2 * n_opt) return;
+    const int opt = o >> 1, which = o & 1;
+    const int chunk = opt / kPayChunk, k = opt % kPayChunk;
+    double t = 0.0;
+    for (int b = 0; b < n_blocks; ++b)
+        t += partials[((size_t)chunk * n_blocks + b) * (2 * kPayChunk) + 2 * k + which];
+    (which ? otm : sums)[opt] = t;
+}
+
+static int payoff_blocks() { return 4 * sm_count(); }
+
+}  // namespace orp
+
+using namespace orp;
+
+extern "C" uint64_t orp_payoff_scratch_bytes(int n_opt) {
+    if (n_opt < 1) n_opt = 1;
+    if (n_opt > ORP_MAX_OPTIONS) n_opt = ORP_MAX_OPTIONS;
+    const int chunks = (n_opt + kPayChunk - 1) / kPayChunk;
+    // sized for the largest grid this library launches on any device it may see (<= 4 blocks x 256 SMs)
+    return (uint64_t)chunks * 1024ull * (2 * kPayChunk) * sizeof(double);
+}
+
+extern "C" int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, uint64_t count, int kind, int n_opt,
+                                 const double* strikes, const int32_t* cols, double s0, double value_scale,
+                                 float* d_values_out, double* d_sums, double* d_otm, void* d_scratch, void* stream) {
+    ORP_REQUIRE(d_paths && strikes && cols && d_sums && d_otm && d_scratch, "null pointer");
+    ORP_REQUIRE(n_opt >= 1 && n_opt <= ORP_MAX_OPTIONS, "n_opt must be in [1, %d]", ORP_MAX_OPTIONS);
+    ORP_REQUIRE(kind >= ORP_PAYOFF_CALL && kind <= ORP_PAYOFF_FLOOR, "unknown payoff kind %d", kind);
+    ORP_REQUIRE(dtype == ORP_F64 || dtype == ORP_F32, "dtype must be ORP_F64 or ORP_F32");
+    ORP_REQUIRE(ld >= count, "ld must be >= count");
+    PayoffArgs a;
+    a.paths = d_paths; a.ld = ld; a.count = count; a.kind = kind; a.n_opt = n_opt;
+    a.s0 = s0; a.value_scale = value_scale; a.values_out = d_values_out;
+    a.partials = reinterpret_cast<double*>(d_scratch);
+    for (int k = 0; k < n_opt; ++k) {
+        ORP_REQUIRE(cols[k] >= 0, "negative column index");
+        a.strikes[k] = strikes[k];
+        a.cols[k] = cols[k];
+    }
+    const int chunks = (n_opt + kPayChunk - 1) / kPayChunk;
+    uint64_t want = (count + kPayThreads - 1) / kPayThreads;
+    if (want < 1) want = 1;
+    int gx = payoff_blocks();
+    if (gx > 1024) gx = 1024;
+    if ((uint64_t)gx > want) gx = (int)want;
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid(gx, chunks);
+    if (dtype == ORP_F64) payoff_partial_kernel<double><<<grid, kPayThreads, 0, st>>>(a);
+    else                  payoff_partial_kernel<float><<<grid, kPayThreads, 0, st>>>(a);
+    ORP_LAUNCH_CHECK("payoff_partial_kernel");
+    payoff_final_kernel<<<(2 * n_opt + 127) / 128, 128, 0, st>>>(a.partials, gx, n_opt, d_sums, d_otm);
+    ORP_LAUNCH_CHECK("payoff_final_kernel");
+    return ORP_OK;
+}

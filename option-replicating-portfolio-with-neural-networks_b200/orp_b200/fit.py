@@ -1,0 +1,202 @@
+"""Backward per-time-step replicating-portfolio fit on the GPU (host driver).
+
+Mirrors the loop ``for t_i in trange(n_time_steps-2, -1, -1)`` of ``Replicating_Portfolio.py:193-227`` and
+``European Options.ipynb`` cell 13 with the Keras semantics of SURVEY.md Appendix B.  Two modes:
+
+* ``mode='scaled'`` (B200-native): one optimiser step per pass over ALL paths of all ranks — the fused
+  forward/backward kernel fills every SM, the ``[gradient, loss, count]`` vector is all-reduced over ranks,
+  Adam / LR schedule / early stopping run on the device so epochs are enqueued without host syncs.
+* ``mode='keras'``: batch_size-512 mini-batches in a shuffled order, serial by definition, one thread block.
+
+Weights, both Adam states and the learning rate persist across time steps exactly as the reference's
+compiled models do (``:175-180, 203-211``).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from .dist import allreduce_sum_, is_distributed
+
+HIDDEN = 8
+NET_IO = {"eo": (1, 1), "rp": (3, 2)}
+
+
+def n_params(net: str) -> int:
+    return _lib.lib().orp_fit_n_params(_lib.NET[net])
+
+
+def init_params(net: str, seed: int, out_bias) -> np.ndarray:
+    """``RandomNormal(0, 0.1)`` kernels, zero hidden biases, constant output bias
+    (``Replicating_Portfolio.py:149-150``; EO cell 12).  TensorFlow's generator cannot be reproduced, so the
+    draw is ours: NumPy PCG64 seeded with ``seed``.  Layout: W1[in][8], b1, W2[8][8], b2, W3[8][out], b3."""
+    i, o = NET_IO[net]
+    rng = np.random.default_rng(seed)
+    w1 = rng.normal(0.0, 0.1, size=(i, HIDDEN))
+    w2 = rng.normal(0.0, 0.1, size=(HIDDEN, HIDDEN))
+    w3 = rng.normal(0.0, 0.1, size=(HIDDEN, o))
+    b3 = np.broadcast_to(np.asarray(out_bias, dtype=np.float64), (o,))
+    return np.concatenate([w1.ravel(), np.zeros(HIDDEN), w2.ravel(), np.zeros(HIDDEN), w3.ravel(), b3]).astype(np.float32)
+
+
+class Optimizer:
+    """Device-resident Adam + callback state of one compiled Keras model (``keras.optimizers.Adam(1e-3)``)."""
+
+    def __init__(self, device):
+        torch = _lib.require_cuda()
+        self.state = torch.empty(_lib.FIT_STATE_DOUBLES, dtype=torch.float64, device=device)
+        with torch.cuda.device(device):
+            _lib.check(_lib.lib().orp_fit_init(_lib.ptr(self.state), _lib.stream_ptr()))
+
+    def head(self) -> np.ndarray:
+        return self.state[:16].cpu().numpy()
+
+
+class ReplicationNet:
+    """The shared weights of model1/model2 plus scratch buffers; ``fit`` runs one ``Model.fit`` call."""
+
+    def __init__(self, net: str, params0: np.ndarray, device="cuda", group=None):
+        torch = _lib.require_cuda()
+        if net not in _lib.NET:
+            raise ValueError(f"net must be one of {sorted(_lib.NET)}")
+        self.net, self.device, self.group = net, torch.device(device), group
+        self.P = n_params(net)
+        if params0.shape != (self.P,):
+            raise ValueError(f"expected {self.P} parameters for net '{net}'")
+        self.params = torch.zeros(_lib.FIT_MAX_PARAMS, dtype=torch.float32, device=self.device)
+        self.params[:self.P] = torch.from_numpy(np.ascontiguousarray(params0, dtype=np.float32)).to(self.device)
+        self.gsum = torch.zeros(_lib.GSUM_LEN, dtype=torch.float64, device=self.device)
+        self.scratch = torch.empty(_lib.lib().orp_fit_scratch_bytes(), dtype=torch.uint8, device=self.device)
+        self.sums = torch.zeros(4, dtype=torch.float64, device=self.device)
+        self.launches = 0
+
+    def batch(self, s_t, s_t1, target, inv_scale, bond_t, bond_t1, loss="mse", feat1=None, feat2=None):
+        torch = _lib.require_cuda()
+        b = _lib.FitBatch()
+        b.net, b.loss = _lib.NET[self.net], _lib.LOSS[loss]
+        b.paths_dtype = _lib.F64 if s_t.dtype == torch.float64 else _lib.F32
+        b.count = s_t.numel()
+        for t in (s_t, s_t1, target, feat1, feat2):
+            if t is not None and not t.is_contiguous():
+                raise ValueError("columns must be contiguous (use the time-major path tensor)")
+        b.d_s_t, b.d_s_t1 = _lib.ptr(s_t), _lib.ptr(s_t1)
+        b.d_feat1, b.d_feat2, b.d_target = _lib.ptr(feat1) or None, _lib.ptr(feat2) or None, _lib.ptr(target) or None
+        b.inv_scale, b.bond_t, b.bond_t1 = float(inv_scale), float(bond_t), float(bond_t1)
+        b._keep = (s_t, s_t1, target, feat1, feat2)          # keep the tensors alive
+        return b
+
+    def fit(self, batch, opt: Optimizer, epochs: int, patience: int, use_schedule: bool, mode: str = "scaled",
+            batch_size: int = 512, shuffle_seed: int = 0, check_every: int = 16):
+        """One ``Model.fit`` (``Replicating_Portfolio.py:211``).  Returns ``dict(epochs_run, loss,
+        stopped_early, lr)``."""
+        torch = _lib.require_cuda()
+        L = _lib.lib()
+        netc = _lib.NET[self.net]
+        with torch.cuda.device(self.device):
+            st = _lib.stream_ptr()
+            _lib.check(L.orp_fit_begin(_lib.ptr(opt.state), int(epochs), int(patience), int(bool(use_schedule)), st))
+            done = 0
+            while done < epochs:
+                n = min(check_every, epochs - done)
+                for e in range(n):
+                    if mode == "scaled":
+                        _lib.check(L.orp_fit_grad(C.byref(batch), _lib.ptr(self.params), _lib.ptr(opt.state),
+                                                  _lib.ptr(self.gsum), _lib.ptr(self.scratch), st))
+                        if is_distributed(self.group):
+                            allreduce_sum_(self.gsum, self.group)
+                        _lib.check(L.orp_fit_update(netc, _lib.ptr(self.params), _lib.ptr(opt.state), _lib.ptr(self.gsum), st))
+                        self.launches += 3
+                    elif mode == "keras":
+                        if is_distributed(self.group):
+                            raise ValueError("mode='keras' is serial by definition: replicas only, no sharding")
+                        _lib.check(L.orp_fit_epoch_minibatch(C.byref(batch), _lib.ptr(self.params), _lib.ptr(opt.state),
+                                                             int(batch_size), int(shuffle_seed) * 1_000_003 + done + e, st))
+                        self.launches += 1
+                    else:
+                        raise ValueError("mode must be 'scaled' or 'keras'")
+                done += n
+                if opt.state[_lib.ST_STOP].item() != 0.0:       # one 8-byte read per `check_every` epochs
+                    break
+            _lib.check(L.orp_fit_end(netc, _lib.ptr(self.params), _lib.ptr(opt.state), st))
+            self.launches += 2
+            h = opt.head()
+        return {"epochs_run": int(h[_lib.ST_EPOCHS_RUN]), "loss": float(h[_lib.ST_LAST_LOSS]),
+                "stopped_early": bool(h[_lib.ST_STOPPED_EARLY]), "lr": float(h[_lib.ST_LR])}
+
+    def predict(self, batch, values_out=None):
+        """``model.predict(X0)`` into ``values_out`` (fp32) and the global sums
+        ``(sum V, sum phi, sum psi, sum |y - V(X1)|)`` as a 4-vector on the host."""
+        torch = _lib.require_cuda()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().orp_fit_predict(C.byref(batch), _lib.ptr(self.params), _lib.ptr(values_out),
+                                                  _lib.ptr(self.sums), _lib.ptr(self.scratch), _lib.stream_ptr()))
+            self.launches += 2
+            allreduce_sum_(self.sums, self.group)
+            return self.sums.cpu().numpy().copy()
+
+
+def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: str = "scaled", scale: float = 1.0,
+                    out_bias=None, init_seed: int = 1234, total_paths: int | None = None, group=None,
+                    epochs_first: int = 500, epochs_next: int = 100, patience_first: int = 50, patience_next: int = 7,
+                    batch_size: int = 512, shuffle_seed: int = 0, features=None, second_model: bool = False,
+                    cost_of_capital: float = 0.1, check_every: int = 16, verbose: bool = False):
+    """Backward replication over all kept columns.
+
+    ``paths_tm``: TIME-MAJOR ``(n_cols, count)`` CUDA tensor of this rank's paths; ``bond``: ``n_cols`` bond
+    prices; ``terminal_values``: fp32 ``(count,)`` CUDA tensor in network units (EO: ``payoff / S0``).
+    ``scale`` = ``ADJUSTMENT_FACTOR`` dividing prices (EO cell 13: ``S0``).  ``features(t_i)`` returns the two
+    extra fp32 inputs of the ``'rp'`` net ``(N_t/N, lambda_t)`` or ``None``.  ``second_model=True`` adds the
+    pinball-loss fit of the SAME weights and the blend ``values = g + cost_of_capital (h - g)``
+    (``Replicating_Portfolio.py:217-221``; the reference's model2 aliases model1's layers).
+
+    Returns ``dict(V0, phi0, psi0, steps=[...], launches)`` in network units."""
+    torch = _lib.require_cuda()
+    n_cols, count = paths_tm.shape
+    device = paths_tm.device
+    bond = np.asarray(bond, dtype=np.float64)
+    if bond.shape != (n_cols,):
+        raise ValueError("bond must have one entry per kept column")
+    tot = torch.tensor([float(count), float(terminal_values.double().sum())], dtype=torch.float64, device=device)
+    allreduce_sum_(tot, group)
+    tot = tot.cpu().numpy()
+    total = float(tot[0]) if total_paths is None else float(total_paths)
+    if out_bias is None:
+        out_bias = tot[1] / total                      # EO cell 12: payoff.mean() / ADJUSTMENT_FACTOR
+    model = ReplicationNet(net, init_params(net, init_seed, out_bias), device, group)
+    opt1 = Optimizer(device)
+    opt2 = Optimizer(device) if second_model else None
+    v_next = terminal_values.contiguous()
+    v_cur = torch.empty_like(v_next)
+    h_buf = torch.empty_like(v_next) if second_model else None
+    steps, first = [], True
+    phi0 = psi0 = v0 = float("nan")
+    for t_i in range(n_cols - 2, -1, -1):
+        f1, f2 = features(t_i) if features is not None else (None, None)
+        common = dict(inv_scale=1.0 / scale, bond_t=bond[t_i], bond_t1=bond[t_i + 1], feat1=f1, feat2=f2)
+        b = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="mse", **common)
+        h = model.fit(b, opt1, epochs_first if first else epochs_next, patience_first if first else patience_next,
+                      use_schedule=first, mode=mode, batch_size=batch_size,
+                      shuffle_seed=shuffle_seed * 4096 + 2 * t_i, check_every=check_every)
+        sums = model.predict(b, v_cur)
+        rec = dict(t_i=t_i, epochs_run=h["epochs_run"], loss=h["loss"], stopped_early=h["stopped_early"],
+                   mean_V=sums[0] / total, phi=sums[1] / total, psi=sums[2] / total, mae=sums[3] / total)
+        if second_model:
+            b2 = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="pinball", **common)
+            h2 = model.fit(b2, opt2, epochs_first if first else epochs_next, patience_first if first else patience_next,
+                           use_schedule=first, mode=mode, batch_size=batch_size,
+                           shuffle_seed=shuffle_seed * 4096 + 2 * t_i + 1, check_every=check_every)
+            sums2 = model.predict(b2, h_buf)
+            v_cur.add_(h_buf - v_cur, alpha=cost_of_capital)     # values = g + cc (h - g)
+            # get_phi_psi_VaR reads the shared 'Phi_Psi' layer after BOTH fits (Replicating_Portfolio.py:104-115)
+            rec.update(epochs_run2=h2["epochs_run"], loss2=h2["loss"], phi=sums2[1] / total, psi=sums2[2] / total,
+                       mean_V=sums[0] / total + cost_of_capital * (sums2[0] - sums[0]) / total)
+        steps.append(rec)
+        if verbose:
+            print(rec)
+        v_next, v_cur = v_cur, v_next
+        phi0, psi0, v0 = rec["phi"], rec["psi"], rec["mean_V"]
+        first = False
+    return {"V0": v0, "phi0": phi0, "psi0": psi0, "steps": steps, "launches": model.launches,
+            "params": model.params[:model.P].cpu().numpy(), "values0": v_next}
