@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""Benchmark of the B200 hot path on BASELINE.json's scaling configuration (configs[4], "C5"):
+
+    2^26 scrambled-Sobol paths x 252 steps, log-Euler GBM (S0 = K = 100, T = 1, r = .05, sigma = .2), fp64,
+    every column materialised, terminal call payoff, full backward replication (252 fits of the 97-parameter
+    net, scaled mode), sharded over N GPUs by contiguous Sobol index ranges (strong scaling: 2^26 paths in total).
+
+One "step" = one pass of the whole pipeline (paths -> payoff -> 252 fits -> V0, phi0, psi0).
+`value` = paths x steps / step time (path-steps/s), whole job, max over ranks.  The JSON line also carries
+the per-stage times, the HBM roofline of the path kernel, the fp32 figure of the fit kernel, the end-to-end
+number through the public API with host-side set-up and H2D/D2H inside the timed region, the sampled clocks
+and a CPU baseline (the reference's NumPy/SciPy path code + the torch-CPU restatement of its Keras fit).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]          # own arm
+    python bench.py --impl reference ...                         # the reference's CPU path, all host threads
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "option-replicating-portfolio-with-neural-networks_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "path-steps/sec"
+CFG = dict(S0=100.0, K=100.0, T=1.0, r=0.05, sigma=0.2, D=252)
+FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12     # SIMT fp32 FMA peak at max clock (not in MEASURED_PEAKS.json)
+FIT_FLOP_PER_SAMPLE = 2 * 315                             # 315 FMA-class ops per sample (EO net, fwd+bwd)
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured"
+    except OSError:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) > 3 + k and r[3 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ own arm
+
+class Pipeline:
+    """One rank's share of the C5 pipeline; buffers are allocated once and reused by every step."""
+
+    def __init__(self, m, D, rank, world, device):
+        import torch
+        import orp_b200
+        self.torch, self.orp = torch, orp_b200
+        self.m, self.D, self.rank, self.world, self.device = m, D, rank, world, device
+        self.start, self.count = orp_b200.shard_range(2 ** m, rank, world)
+        self.sim = dict(S0=CFG["S0"], mu=CFG["r"], sigma=CFG["sigma"], dt=CFG["T"] / D)
+        self.paths = torch.empty((D + 1, self.count), dtype=torch.float64, device=device)
+        self.vals = torch.empty(self.count, dtype=torch.float32, device=device)
+        self.bond = orp_b200.bond_curve(CFG["r"], CFG["T"], D + 1)
+        self.ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+
+    def step(self, fresh_engine=False):
+        torch, orp = self.torch, self.orp
+        if fresh_engine:                       # e2e: host-side set-up and the H2D of its tables are inside the timed region
+            from orp_b200 import sobol
+            sobol.engine.cache_clear()
+        self.ev[0].record()
+        orp.simulate_paths("gbm_log", self.sim, steps=self.D, start=self.start, count=self.count, out=self.paths,
+                           device=self.device, time_major=True)
+        self.ev[1].record()
+        sums, otm = orp.payoff_sums(self.paths, [CFG["K"]], [-1], "call", values_out=self.vals, value_scale=1.0 / CFG["S0"])
+        self.ev[2].record()
+        res = orp.fit_replication(self.paths, self.bond, self.vals, net="eo", scale=CFG["S0"], total_paths=2 ** self.m)
+        self.ev[3].record()
+        est = torch.stack([sums[0], otm[0]])
+        orp.dist.allreduce_sum_(est)
+        est = est.cpu().numpy()                # D2H of the step's result
+        self.ev[3].synchronize()
+        t = [self.ev[i].elapsed_time(self.ev[i + 1]) for i in range(3)]
+        return dict(price_mc=float(np.exp(-CFG["r"] * CFG["T"]) * est[0] / 2 ** self.m), p_otm=float(est[1] / 2 ** self.m),
+                    V0=res["V0"] * CFG["S0"], phi0=res["phi0"], psi0=res["psi0"], launches=3 + res["launches"],
+                    epochs=sum(s["epochs_run"] for s in res["steps"]), t_paths_ms=t[0], t_payoff_ms=t[1], t_fit_ms=t[2])
+
+
+def cpu_baseline(m_sample, D, threads=1, batch_size=512):
+    """The reference's CPU path on a bounded sample of the same workload: NumPy/SciPy path code (oracle.paths,
+    a line-for-line restatement pinned bit-exactly to the reference's arrays) + payoff + the torch-CPU
+    restatement of the Keras loop (batch 512, as the reference runs it)."""
+    import torch
+    from oracle import fit as ofit, paths as opaths
+    torch.set_num_threads(threads)
+    n = 2 ** m_sample
+    t0 = time.perf_counter()
+    sim = dict(S0=CFG["S0"], mu=CFG["r"], sigma=CFG["sigma"], dt=CFG["T"] / D)
+    if threads > 1 and n >= 4 * 4096:
+        import multiprocessing as mp
+        chunks = [(s, min(4096, n - s)) for s in range(0, n, 4096)]
+        with mp.get_context("fork").Pool(min(threads, len(chunks))) as pool:
+            S = np.concatenate(pool.starmap(_cpu_chunk, [(sim, D, s, c) for s, c in chunks]), axis=0)
+    else:
+        S = opaths.simulate_window("gbm_log", sim, D + 1, 0, n)
+    t_paths = time.perf_counter() - t0
+    pay = opaths.payoff(S[:, -1], CFG["K"], "call")
+    bond = opaths.bond_curve(CFG["r"], CFG["T"], D + 1)
+    res = ofit.backward_replication(S, bond, pay / CFG["S0"], net="eo", scale=CFG["S0"], batch_size=batch_size)
+    t = time.perf_counter() - t0
+    return dict(value=n * D / t, seconds=t, seconds_paths=t_paths, V0=res["V0"] * CFG["S0"],
+                price_mc=float(np.exp(-CFG["r"] * CFG["T"]) * pay.mean()),
+                sample=f"2^{m_sample} of the 2^26 paths x {D} steps, same pipeline (paths + payoff + {D} fits, batch {batch_size})")
+
+
+def _cpu_chunk(sim, D, start, count):
+    from oracle import paths as opaths
+    return opaths.simulate_window("gbm_log", sim, D + 1, start, count)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    D = args.path_steps
+    times = []
+    for i in range(args.warmup + args.steps):
+        r = cpu_baseline(args.ref_sample_m, D, threads=cores)
+        if i >= args.warmup:
+            times.append(r["seconds"])
+    ms = 1e3 * float(np.mean(times))
+    value = 2 ** args.ref_sample_m * D / (ms / 1e3)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "path-steps/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(args.m, D), "paths_log2": args.m, "path_steps": D,
+                       "note": "each step is a bounded sample of the workload"},
+            "cpu_baseline": {"value": value, "unit": "path-steps/s", "cores": cores, "kind": "port", "sample": r["sample"]},
+            "e2e": {"value": value, "unit": "path-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "check": {"V0": r["V0"], "price_mc": r["price_mc"]}}
+    print(json.dumps(line))
+    return 0
+
+
+def workload_name(m, D):
+    return (f"C5: 2^{m} Sobol paths x {D} steps log-Euler GBM fp64 (S0=K=100,T=1,r=.05,sigma=.2), all columns stored, "
+            f"call payoff, full backward replication ({D} fits, EO net, scaled mode)")
+
+
+def run_own(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    m, D = args.m, args.path_steps
+    pipe = Pipeline(m, D, rank, world, device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        last = pipe.step()
+    sampler = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    t0 = time.perf_counter()
+    stages = []
+    for _ in range(args.steps):
+        last = pipe.step()
+        stages.append(last)
+    barrier()
+    elapsed = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    # end to end: host-side engine set-up + H2D of its tables + pipeline + D2H of the results, every step
+    barrier()
+    t1 = time.perf_counter()
+    n_e2e = max(1, min(args.steps, 2))
+    for _ in range(n_e2e):
+        pipe.step(fresh_engine=True)
+    barrier()
+    e2e_elapsed = (time.perf_counter() - t1) / n_e2e
+    tt = torch.tensor([elapsed, e2e_elapsed], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    elapsed, e2e_elapsed = (float(x) for x in tt.cpu())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    ms = 1e3 * elapsed / args.steps
+    total_steps = 2 ** m * D
+    peaks, peak_kind = measured_peaks()
+    t_paths = float(np.mean([s["t_paths_ms"] for s in stages]))
+    t_fit = float(np.mean([s["t_fit_ms"] for s in stages]))
+    t_pay = float(np.mean([s["t_payoff_ms"] for s in stages]))
+    path_bytes = pipe.count * (D + 1) * 8                      # algorithmic bytes: one fp64 store per kept column (incl. column 0)
+    achieved = path_bytes / (t_paths * 1e-3) / 1e9
+    epochs = last["epochs"]
+    fit_flops = 2 ** m / world * epochs * FIT_FLOP_PER_SAMPLE
+    from orp_b200 import sobol
+    eng = sobol.engine(D + 1, 1235)
+    line = {
+        "metric": METRIC, "value": total_steps / (ms / 1e3), "unit": "path-steps/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(m, D), "paths_log2": m, "path_steps": D, "parallelism": f"paths sharded x{world} by Sobol index range",
+                   "l2": "inputs larger than L2 (the path array is read back by the fits; >= 16 GB per GPU)"},
+        "roofline": {"kernel": "paths_kernel<GBM_LOG,double>", "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
+                     "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_kind": peak_kind + " (burst copy figure)",
+                     "algorithmic_bytes_per_launch": path_bytes, "ms_per_launch": t_paths},
+        "fit_kernel": {"bound": "fp32 SIMT issue", "tflops": fit_flops / (t_fit * 1e-3) / 1e12, "peak_nominal_tflops": FP32_NOMINAL_TFLOPS,
+                       "epochs_per_step": epochs, "samples_per_s": 2 ** m / world * epochs / (t_fit * 1e-3)},
+        "stages_ms": {"paths": t_paths, "payoff": t_pay, "fit": t_fit},
+        "path_stage_path_steps_per_s": total_steps / world / (t_paths * 1e-3) * world,
+        "e2e": {"value": total_steps / e2e_elapsed, "unit": "path-steps/s", "h2d_bytes_per_step": int(eng.sv32.nbytes + eng.tlane.nbytes),
+                "d2h_bytes_per_step": int(16 + 16 * 8 * (D + 2) + 32 * D)},
+        "gpu_launches": int(sum(s["launches"] for s in stages)),
+        "clocks": clocks,
+        "result": {"V0_nn": last["V0"], "phi0": last["phi0"], "psi0": last["psi0"], "price_mc": last["price_mc"], "p_otm": last["p_otm"]},
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cb = cpu_baseline(args.cpu_sample_m, D, threads=1)
+        line["cpu_baseline"] = {"value": cb["value"], "unit": "path-steps/s", "cores": 1, "kind": "port", "sample": cb["sample"],
+                                "seconds": cb["seconds"], "paths_only_path_steps_per_s": 2 ** args.cpu_sample_m * D / cb["seconds_paths"]}
+        from oracle import paths as opaths
+        line["result"]["black_scholes"] = opaths.black_scholes_call(CFG["S0"], CFG["K"], CFG["T"], CFG["r"], CFG["sigma"])
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--m", type=int, default=26, help="log2 of the total path count (BASELINE C5: 26)")
+    ap.add_argument("--path-steps", type=int, default=CFG["D"], help="time steps per path (BASELINE C5: 252)")
+    ap.add_argument("--cpu-sample-m", type=int, default=12)
+    ap.add_argument("--ref-sample-m", type=int, default=11)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    return run_reference(args) if args.impl == "reference" else run_own(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -69,7 +69,7 @@ int orp_ndtri_u32(const uint32_t* d_x, uint64_t n, double* d_z, void* stream);
 
 /* ---------------------------------------------------------------- a-4/5/8  paths (device) */
 
-enum { ORP_MODEL_GBM_LOG = 0, ORP_MODEL_GBM_ARITH = 1, ORP_MODEL_SV = 2 };
+enum { ORP_MODEL_GBM_LOG = 0, ORP_MODEL_GBM_ARITH = 1, ORP_MODEL_SV = 2, ORP_MODEL_LINEAR = 3 };
 enum { ORP_ORDER_INCREMENTAL = 0, ORP_ORDER_BRIDGE = 1 };
 enum { ORP_F64 = 0, ORP_F32 = 1 };
 
@@ -91,6 +91,7 @@ typedef struct orp_path_params {
  *   GBM_ARITH  Replicating_Portfolio.py:60-65, 93
  *   GBM_LOG    European Options.ipynb cell 6 (raw 156-165) and cell 7 (raw 205-207)
  *   SV         Replicating_Portfolio.py:274-289, 93   (second engine d_sv32_b/d_tlane_b drives the volatility)
+ *   LINEAR     Replicating_Portfolio.py:72-76 (mortality intensity: mu = c, sigma = ita, s0 = l0)
  * Output is TIME-MAJOR: d_out[col * ld + (i - start)], col = t / keep_every, 0 <= col <= D / keep_every, ld >= count.
  * d_bridge: device schedule from orp_bridge_schedule (ordering = BRIDGE) or NULL. */
 int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const uint32_t* d_tlane,

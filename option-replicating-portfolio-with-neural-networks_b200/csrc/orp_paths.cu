@@ -97,6 +97,9 @@ __device__ __forceinline__ void store_col(void* out, uint64_t ld, int col, uint6
     reinterpret_cast<OutT*>(out)[(size_t)col * ld + j] = (OutT)v;
 }
 
+// models whose state is the level itself (no exp at the kept columns)
+template <int MODEL> constexpr bool kLevel = MODEL == ORP_MODEL_GBM_ARITH || MODEL == ORP_MODEL_LINEAR;
+
 // One time step for the two paths of a lane.  z: normals of the price engine, y: of the volatility engine.
 template <int MODEL>
 __device__ __forceinline__ void advance(const PathArgs& a, double& s_0, double& s_1, double& v_0, double& v_1,
@@ -109,6 +112,10 @@ __device__ __forceinline__ void advance(const PathArgs& a, double& s_0, double& 
         // Y_t = Y_{t-1} + Y_{t-1} (mu dt + sigma sqrt(dt) W_t)                                RP.py:65
         s_0 = fma(s_0, fma(a.c_vol, z0, a.c_drift), s_0);
         s_1 = fma(s_1, fma(a.c_vol, z1, a.c_drift), s_1);
+    } else if (MODEL == ORP_MODEL_LINEAR) {
+        // l_t = l_{t-1} + (c l_{t-1} dt + ita sqrt(dt) W_t)                                    RP.py:76
+        s_0 += fma(a.c_vol, z0, s_0 * a.c_drift);
+        s_1 += fma(a.c_vol, z1, s_1 * a.c_drift);
     } else {
         // v_t = v + a (b - v) + c sqrt(v dt) Wv_t;  lnY_t = lnY + ((mu - v_t^2/2) dt + v_t sqrt(dt) W_t)   RP.py:285-287
         v_0 = (v_0 + a.a * (a.b - v_0)) + (a.c * sqrt(v_0 * a.dt)) * y0;
@@ -140,7 +147,7 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
 
         // state: GBM_LOG ln S; GBM_ARITH S; SV ln Y and v
         double s_0, s_1, v_0 = a.v0, v_1 = a.v0;
-        if (MODEL == ORP_MODEL_GBM_ARITH) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
+        if (kLevel<MODEL>) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
         if (ok0) store_col<OutT>(a.out, a.ld, 0, j0, a.s0);
         if (ok1) store_col<OutT>(a.out, a.ld, 0, j1, a.s0);
         int next_keep = a.keep_every, col = 1;
@@ -169,7 +176,7 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
                 advance<MODEL>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
                 if (t == next_keep) {
                     double o0 = s_0, o1 = s_1;
-                    if (MODEL != ORP_MODEL_GBM_ARITH) { o0 = exp(s_0); o1 = exp(s_1); }
+                    if (!kLevel<MODEL>) { o0 = exp(s_0); o1 = exp(s_1); }
                     if (ok0) store_col<OutT>(a.out, a.ld, col, j0, o0);
                     if (ok1) store_col<OutT>(a.out, a.ld, col, j1, o1);
                     next_keep += a.keep_every;
@@ -212,7 +219,7 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
         const uint64_t j0 = i0 - a.start, j1 = i1 - a.start;
 
         double s_0, s_1, v_0 = a.v0, v_1 = a.v0;
-        if (MODEL == ORP_MODEL_GBM_ARITH) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
+        if (kLevel<MODEL>) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
         if (ok0) store_col<OutT>(a.out, a.ld, 0, j0, a.s0);
         if (ok1) store_col<OutT>(a.out, a.ld, 0, j1, a.s0);
         int next_keep = a.keep_every, col = 1, t = 0, sp = -1;
@@ -260,7 +267,7 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
                     advance<MODEL>(a, s_0, s_1, v_0, v_1, inc[0], inc[1], inc[NS - 2], inc[NS - 1]);
                     if (t == next_keep) {
                         double q0 = s_0, q1 = s_1;
-                        if (MODEL != ORP_MODEL_GBM_ARITH) { q0 = exp(s_0); q1 = exp(s_1); }
+                        if (!kLevel<MODEL>) { q0 = exp(s_0); q1 = exp(s_1); }
                         if (ok0) store_col<OutT>(a.out, a.ld, col, j0, q0);
                         if (ok1) store_col<OutT>(a.out, a.ld, col, j1, q1);
                         next_keep += a.keep_every;
@@ -417,12 +424,14 @@ extern "C" int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const
         case ORP_MODEL_GBM_LOG:   a.c_drift = (p->mu - 0.5 * p->sigma * p->sigma) * p->dt; a.c_vol = p->sigma * sqdt; break;
         case ORP_MODEL_GBM_ARITH: a.c_drift = p->mu * p->dt;                              a.c_vol = p->sigma * sqdt; break;
         case ORP_MODEL_SV:        a.c_drift = p->mu;                                      a.c_vol = sqdt;            break;
+        case ORP_MODEL_LINEAR:    a.c_drift = p->mu * p->dt;                              a.c_vol = p->sigma * sqdt; break;
         default: return fail(ORP_E_VALUE, "unknown model %d", p->model);
     }
     if (p->ordering == ORP_ORDER_BRIDGE) {
         switch (p->model) {
             case ORP_MODEL_GBM_LOG:   return p->out_dtype == ORP_F32 ? launch_paths_bridge<ORP_MODEL_GBM_LOG, float>(a, d_bridge, (cudaStream_t)stream)   : launch_paths_bridge<ORP_MODEL_GBM_LOG, double>(a, d_bridge, (cudaStream_t)stream);
             case ORP_MODEL_GBM_ARITH: return p->out_dtype == ORP_F32 ? launch_paths_bridge<ORP_MODEL_GBM_ARITH, float>(a, d_bridge, (cudaStream_t)stream) : launch_paths_bridge<ORP_MODEL_GBM_ARITH, double>(a, d_bridge, (cudaStream_t)stream);
+            case ORP_MODEL_LINEAR:    return p->out_dtype == ORP_F32 ? launch_paths_bridge<ORP_MODEL_LINEAR, float>(a, d_bridge, (cudaStream_t)stream)    : launch_paths_bridge<ORP_MODEL_LINEAR, double>(a, d_bridge, (cudaStream_t)stream);
             default:                  return p->out_dtype == ORP_F32 ? launch_paths_bridge<ORP_MODEL_SV, float>(a, d_bridge, (cudaStream_t)stream)        : launch_paths_bridge<ORP_MODEL_SV, double>(a, d_bridge, (cudaStream_t)stream);
         }
     }
@@ -431,6 +440,7 @@ extern "C" int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const
     switch (p->model) {
         case ORP_MODEL_GBM_LOG:   return f32 ? launch_paths<ORP_MODEL_GBM_LOG, float>(a, st)   : launch_paths<ORP_MODEL_GBM_LOG, double>(a, st);
         case ORP_MODEL_GBM_ARITH: return f32 ? launch_paths<ORP_MODEL_GBM_ARITH, float>(a, st) : launch_paths<ORP_MODEL_GBM_ARITH, double>(a, st);
+        case ORP_MODEL_LINEAR:    return f32 ? launch_paths<ORP_MODEL_LINEAR, float>(a, st)    : launch_paths<ORP_MODEL_LINEAR, double>(a, st);
         default:                  return f32 ? launch_paths<ORP_MODEL_SV, float>(a, st)        : launch_paths<ORP_MODEL_SV, double>(a, st);
     }
 }

@@ -14,7 +14,7 @@ _PKG = os.path.dirname(_HERE)
 LIB_PATH = os.path.join(_PKG, "liborp_b200.so")
 
 ORP_OK, ORP_E_VALUE, ORP_E_CUDA, ORP_E_STATE = 0, -1, -2, -3
-MODEL = {"gbm_log": 0, "gbm_arith": 1, "gbm_euler": 1, "sv": 2}
+MODEL = {"gbm_log": 0, "gbm_arith": 1, "gbm_euler": 1, "sv": 2, "linear": 3}
 ORDER = {"incremental": 0, "bridge": 1}
 PAYOFF = {"call": 0, "put": 1, "floor": 2}
 NET = {"eo": 0, "rp": 1}

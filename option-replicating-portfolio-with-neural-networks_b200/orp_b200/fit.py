@@ -141,7 +141,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
                     out_bias=None, init_seed: int = 1234, total_paths: int | None = None, group=None,
                     epochs_first: int = 500, epochs_next: int = 100, patience_first: int = 50, patience_next: int = 7,
                     batch_size: int = 512, shuffle_seed: int = 0, features=None, second_model: bool = False,
-                    cost_of_capital: float = 0.1, check_every: int = 16, verbose: bool = False):
+                    cost_of_capital: float = 0.1, check_every: int = 16, verbose: bool = False, on_step=None):
     """Backward replication over all kept columns.
 
     ``paths_tm``: TIME-MAJOR ``(n_cols, count)`` CUDA tensor of this rank's paths; ``bond``: ``n_cols`` bond
@@ -173,6 +173,8 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
     steps, first = [], True
     phi0 = psi0 = v0 = float("nan")
     for t_i in range(n_cols - 2, -1, -1):
+        if on_step is not None:
+            on_step({"t_i": t_i})
         f1, f2 = features(t_i) if features is not None else (None, None)
         common = dict(inv_scale=1.0 / scale, bond_t=bond[t_i], bond_t1=bond[t_i + 1], feat1=f1, feat2=f2)
         b = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="mse", **common)

@@ -62,12 +62,13 @@ def bridge_schedule_host(n_steps: int) -> np.ndarray:
 def simulate_paths(model: str, params: dict, m: int | None = None, steps: int | None = None, seed: int = 1235,
                    ordering: str = "incremental", dtype: str = "float64", keep_every: int = 1,
                    shard=(0, 1), start: int | None = None, count: int | None = None, seed_sv: int = 1234,
-                   device="cuda", out=None, time_major: bool = False):
+                   device="cuda", out=None, time_major: bool = False, engine_dim: int | None = None):
     """Simulate ``count`` paths of ``steps`` fine steps and keep every ``keep_every``-th column.
 
     ``model``: ``'gbm_log'`` (EO cell 6), ``'gbm_arith'``/``'gbm_euler'`` (``Replicating_Portfolio.py:65``),
     ``'sv'`` (``:285-287``).  ``params``: ``S0`` (or ``Y``), ``mu`` (or ``r``), ``sigma``, ``dt``; for ``'sv'``
-    ``s0, a, b, c``.  The engines have ``d = steps + 1`` dimensions and seeds 1235 (price) / 1234
+    ``s0, a, b, c``; ``'linear'`` (``:76``) takes ``S0=l0, mu=c, sigma=ita``.  The engines have ``d = steps + 1`` dimensions
+    (``engine_dim`` overrides it when fewer steps than the reference's grid are run) and seeds 1235 (price) / 1234
     (volatility) as in the reference.  Index range: ``[start, start+count)`` or the ``shard=(rank, world)``
     slice of ``2**m`` paths.
 
@@ -92,7 +93,9 @@ def simulate_paths(model: str, params: dict, m: int | None = None, steps: int | 
     keep_every = int(keep_every)
     if keep_every < 1:
         raise ValueError("keep_every must be >= 1")
-    d = steps + 1
+    d = steps + 1 if engine_dim is None else int(engine_dim)     # the reference's d = n_time_steps
+    if steps > d - 1:
+        raise ValueError("steps must be <= engine_dim - 1")
     n_cols = steps // keep_every + 1
     device = torch.device(device)
     p = _lib.PathParams()

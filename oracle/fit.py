@@ -111,7 +111,7 @@ class AdamState:
 
 def fit(params: torch.Tensor, opt: AdamState, net: str, x, prices, y, *, epochs: int,
         patience: int, use_schedule: bool, loss: str = "mse", batch_size=512,
-        shuffle_rng=None):
+        shuffle_rng=None, perm_fn=None):
     """One Keras ``model.fit`` call (``Replicating_Portfolio.py:211``), in place on ``params``.
 
     ``batch_size=None`` is the scaled mode of the CUDA path: one full-batch Adam step per epoch,
@@ -128,7 +128,10 @@ def fit(params: torch.Tensor, opt: AdamState, net: str, x, prices, y, *, epochs:
         if batch_size is None:
             batches = [slice(None)]
         else:
-            perm = torch.from_numpy(shuffle_rng.permutation(n)) if shuffle_rng is not None else torch.arange(n)
+            if perm_fn is not None:
+                perm = torch.from_numpy(perm_fn(epoch))
+            else:
+                perm = torch.from_numpy(shuffle_rng.permutation(n)) if shuffle_rng is not None else torch.arange(n)
             batches = [perm[s:s + batch_size] for s in range(0, n, batch_size)]
         tot = 0.0
         for idx in batches:
@@ -138,7 +141,7 @@ def fit(params: torch.Tensor, opt: AdamState, net: str, x, prices, y, *, epochs:
             (g,) = torch.autograd.grad(l, p)
             opt.step(params, g)
             nb = n if batch_size is None else len(idx)
-            tot += float(l) * nb
+            tot += float(l.detach()) * nb
         cur = tot / n
         losses.append(cur)
         wait += 1
@@ -152,12 +155,43 @@ def fit(params: torch.Tensor, opt: AdamState, net: str, x, prices, y, *, epochs:
     return {"epochs_run": len(losses), "losses": losses, "stopped_early": stopped}
 
 
+M64 = (1 << 64) - 1
+
+
+def perm_pow2(x: int, bits: int, seed: int) -> int:
+    """The epoch permutation of the CUDA mini-batch kernel (``perm_pow2`` in ``csrc/orp_fit.cu``):
+    odd multiply, xorshift, odd multiply on ``bits`` bits.  Ours, not Keras' (its shuffle is not
+    reproducible); restated here so both sides visit samples in the same order."""
+    mask = (1 << bits) - 1
+    a1 = ((seed * 0x9E3779B97F4A7C15) & M64) | 1
+    a2 = (((seed ^ 0xD1B54A32D192ED03) * 0xBF58476D1CE4E5B9) & M64) | 1
+    x = ((x * a1 + (seed >> 7)) & M64) & mask
+    x ^= x >> ((bits + 1) // 2)
+    x = ((x * a2) & M64) & mask
+    x ^= x >> ((bits + 2) // 3)
+    return x & mask
+
+
+def minibatch_perm(n: int, seed: int) -> np.ndarray:
+    """Sample order of one epoch: position -> sample index (cycle-walking below ``n``)."""
+    bits = 0
+    while (1 << bits) < n:
+        bits += 1
+    out = np.empty(n, dtype=np.int64)
+    for pos in range(n):
+        i = perm_pow2(pos, bits, seed)
+        while i >= n:
+            i = perm_pow2(i, bits, seed)
+        out[pos] = i
+    return out
+
+
 def backward_replication(S_cols: np.ndarray, B_cols: np.ndarray, terminal_value: np.ndarray, *,
                          net: str = "eo", scale: float = 1.0, init_seed: int = 1234,
                          out_bias=None, batch_size=512, shuffle_seed: int = 0,
                          epochs_first: int = 500, epochs_next: int = 100,
                          patience_first: int = 50, patience_next: int = 7,
-                         features=None):
+                         features=None, cuda_perm: bool = False):
     """The loop ``for t_i in range(n-2, -1, -1)`` of ``European Options.ipynb`` cell 13 (model1
     only, ``values[:, t_i] = g_t``); with ``net='rp'`` the MSE half of
     ``Replicating_Portfolio.py:193-221``.
@@ -192,7 +226,9 @@ def backward_replication(S_cols: np.ndarray, B_cols: np.ndarray, terminal_value:
         y = torch.from_numpy(values[:, t_i + 1].astype(np.float32))
         h = fit(params, opt, net, x, p1, y, epochs=epochs_first if first else epochs_next,
                 patience=patience_first if first else patience_next, use_schedule=first,
-                batch_size=batch_size, shuffle_rng=rng)
+                batch_size=batch_size, shuffle_rng=rng,
+                perm_fn=(lambda e, t_i=t_i: minibatch_perm(n_paths, (shuffle_seed * 4096 + 2 * t_i) * 1_000_003 + e))
+                if (cuda_perm and batch_size is not None) else None)
         with torch.no_grad():
             g_t, phi, psi = forward(params, net, x, p0)
         values[:, t_i] = g_t.numpy().astype(np.float64)

@@ -1,0 +1,184 @@
+"""GPU parity tests of the replicating-portfolio fit (through the C ABI) against the torch-CPU oracle.
+
+Bit-level fit parity with the reference is impossible (TensorFlow's RNG; TF not installed): the oracle is the
+restatement in oracle/fit.py fed with the SAME initial weights, inputs and sample order.  Tolerances (fp32
+arithmetic, different summation order): one-step gradients 2e-4 relative to the gradient's max-norm; weights
+after a few optimiser steps 2e-3 absolute (Adam divides by sqrt(v), so early steps amplify rounding);
+end-to-end t=0 price 2 % of the oracle's (the seed-to-seed spread of the method itself is ~10 %)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import fit as ofit, paths as opaths
+
+pytestmark = pytest.mark.gpu
+
+
+def _toy(n, seed=0, net="eo"):
+    rng = np.random.default_rng(seed)
+    s_t = 100.0 * np.exp(0.2 * rng.standard_normal(n))
+    s_t1 = s_t * np.exp(0.03 * rng.standard_normal(n))
+    y = (np.maximum(s_t1 - 100.0, 0) / 100.0).astype(np.float32)
+    f1 = (1.0 - 0.01 * rng.random(n)).astype(np.float32)
+    f2 = (0.01 + 0.001 * rng.standard_normal(n)).astype(np.float32)
+    return s_t, s_t1, y, f1, f2
+
+
+def _oracle_inputs(net, s_t, s_t1, y, f1, f2, scale, b_t, b_t1):
+    st = torch.from_numpy((s_t / scale).astype(np.float32))
+    st1 = torch.from_numpy((s_t1 / scale).astype(np.float32))
+    x = st[:, None] if net == "eo" else torch.stack([st, torch.from_numpy(f1), torch.from_numpy(f2)], dim=1)
+    p0 = torch.stack([st, torch.full_like(st, np.float32(b_t / scale))], dim=1)
+    p1 = torch.stack([st1, torch.full_like(st, np.float32(b_t1 / scale))], dim=1)
+    return x, p0, p1, torch.from_numpy(y)
+
+
+@pytest.mark.parametrize("net", ["eo", "rp"])
+@pytest.mark.parametrize("loss", ["mse", "pinball"])
+@pytest.mark.parametrize("n", [1, 1000, 70_001])
+def test_gradient_and_loss_match_autograd(cuda, net, loss, n):
+    from orp_b200 import _lib
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    s_t, s_t1, y, f1, f2 = _toy(n, 1, net)
+    scale, b_t, b_t1 = 100.0, 1.02, 1.03
+    p0 = init_params(net, 7, 0.1 if net == "eo" else [0.9, 0.1])
+    p0 += np.random.default_rng(3).normal(0, 0.2, p0.shape).astype(np.float32)      # leave the symmetric start
+    model = ReplicationNet(net, p0, cuda)
+    opt = Optimizer(cuda)
+    dev = lambda a: torch.from_numpy(a).to(cuda)
+    b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / scale, b_t, b_t1, loss=loss,
+                    feat1=dev(f1) if net == "rp" else None, feat2=dev(f2) if net == "rp" else None)
+    L = _lib.lib()
+    _lib.check(L.orp_fit_begin(_lib.ptr(opt.state), 5, 5, 0, _lib.stream_ptr()))
+    _lib.check(L.orp_fit_grad(C.byref(b), _lib.ptr(model.params), _lib.ptr(opt.state), _lib.ptr(model.gsum),
+                              _lib.ptr(model.scratch), _lib.stream_ptr()))
+    g = model.gsum.cpu().numpy()
+    assert g[_lib.FIT_MAX_PARAMS + 1] == n
+    x, _, p1, yt = _oracle_inputs(net, s_t, s_t1, y, f1, f2, scale, b_t, b_t1)
+    w = torch.from_numpy(p0.copy()).double().requires_grad_(True)
+    v, _, _ = ofit.forward(w, net, x.double(), p1.double())
+    l = ofit.loss_fn(loss, yt.double(), v)
+    (gr,) = torch.autograd.grad(l, w)
+    P = model.P
+    np.testing.assert_allclose(g[_lib.FIT_MAX_PARAMS] / n, float(l), rtol=2e-5, atol=1e-9)
+    ref = gr.numpy()
+    assert np.abs(g[:P] / n - ref).max() <= 2e-4 * max(np.abs(ref).max(), 1e-6)
+
+
+@pytest.mark.parametrize("net", ["eo", "rp"])
+def test_scaled_fit_tracks_oracle(cuda, net):
+    """40 full-batch epochs with the LR schedule: weights, epoch losses and callbacks follow the oracle."""
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    n = 8192
+    s_t, s_t1, y, f1, f2 = _toy(n, 2, net)
+    scale, b_t, b_t1 = 100.0, 1.02, 1.03
+    bias = 0.1 if net == "eo" else [0.9, 0.1]
+    p0 = init_params(net, 1234, bias)
+    model = ReplicationNet(net, p0, cuda)
+    opt = Optimizer(cuda)
+    dev = lambda a: torch.from_numpy(a).to(cuda)
+    b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / scale, b_t, b_t1,
+                    feat1=dev(f1) if net == "rp" else None, feat2=dev(f2) if net == "rp" else None)
+    h = model.fit(b, opt, epochs=40, patience=50, use_schedule=True, mode="scaled")
+    x, p0t, p1, yt = _oracle_inputs(net, s_t, s_t1, y, f1, f2, scale, b_t, b_t1)
+    w = torch.from_numpy(p0.copy())
+    oopt = ofit.AdamState(w.numel())
+    oh = ofit.fit(w, oopt, net, x, p1, yt, epochs=40, patience=50, use_schedule=True, batch_size=None)
+    assert h["epochs_run"] == oh["epochs_run"] == 40 and not h["stopped_early"]
+    assert abs(h["loss"] / oh["losses"][-1] - 1) < 2e-2
+    np.testing.assert_allclose(model.params[:model.P].cpu().numpy(), w.numpy(), atol=2e-3)
+    # predict / roll-back sums
+    vals = torch.empty(n, dtype=torch.float32, device=cuda)
+    sums = model.predict(b, vals)
+    with torch.no_grad():
+        v0, phi, psi = ofit.forward(w, net, x, p0t)
+    np.testing.assert_allclose(vals.cpu().numpy(), v0.numpy(), atol=2e-3)
+    np.testing.assert_allclose(sums[:3] / n, [v0.double().mean(), phi.double().mean(), psi.double().mean()], atol=2e-3)
+
+
+def test_early_stopping_and_restore(cuda):
+    """Constant target reached quickly: the stop fires after `patience` non-improving epochs, the best weights
+    come back, later enqueued epochs are no-ops (device-side control block)."""
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    n = 4096
+    s_t, s_t1, y, _, _ = _toy(n, 5)
+    p0 = init_params("eo", 11, float(y.mean()))
+    model = ReplicationNet("eo", p0, cuda)
+    opt = Optimizer(cuda)
+    dev = lambda a: torch.from_numpy(a).to(cuda)
+    b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / 100.0, 1.0, 1.0)
+    h = model.fit(b, opt, epochs=400, patience=5, use_schedule=True, mode="scaled", check_every=64)
+    x, _, p1, yt = _oracle_inputs("eo", s_t, s_t1, y, None, None, 100.0, 1.0, 1.0)
+    w = torch.from_numpy(p0.copy())
+    oh = ofit.fit(w, ofit.AdamState(w.numel()), "eo", x, p1, yt, epochs=400, patience=5, use_schedule=True, batch_size=None)
+    assert h["stopped_early"] == oh["stopped_early"]
+    assert abs(h["epochs_run"] - oh["epochs_run"]) <= 3          # fp32 noise can move the stopping epoch slightly
+    assert h["epochs_run"] < 400
+
+
+def test_keras_mode_minibatch_tracks_oracle(cuda):
+    """Batch-512 serial mode with the shared permutation: 3 epochs of 8 Adam steps each."""
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    n = 4000                                    # not a multiple of 512: ragged last batch + cycle-walking
+    s_t, s_t1, y, _, _ = _toy(n, 8)
+    p0 = init_params("eo", 1234, float(y.mean()))
+    model = ReplicationNet("eo", p0, cuda)
+    opt = Optimizer(cuda)
+    dev = lambda a: torch.from_numpy(a).to(cuda)
+    b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / 100.0, 1.0, 1.01)
+    h = model.fit(b, opt, epochs=3, patience=50, use_schedule=True, mode="keras", batch_size=512, shuffle_seed=9)
+    x, _, p1, yt = _oracle_inputs("eo", s_t, s_t1, y, None, None, 100.0, 1.0, 1.01)
+    w = torch.from_numpy(p0.copy())
+    oh = ofit.fit(w, ofit.AdamState(w.numel()), "eo", x, p1, yt, epochs=3, patience=50, use_schedule=True,
+                  batch_size=512, perm_fn=lambda e: ofit.minibatch_perm(n, 9 * 1_000_003 + e))
+    assert h["epochs_run"] == 3
+    assert abs(h["loss"] / oh["losses"][-1] - 1) < 5e-2
+    np.testing.assert_allclose(model.params[:model.P].cpu().numpy(), w.numpy(), atol=5e-3)
+
+
+def test_backward_replication_c1(cuda):
+    """BASELINE config C1 (2^16 Sobol paths, single time step, stock+bond NN replication), scaled mode,
+    against the oracle's full-batch restatement on the same paths."""
+    import orp_b200
+    p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 252)
+    m, D = 16, 252
+    tm = orp_b200.simulate_paths("gbm_log", p, m=m, steps=D, keep_every=D, time_major=True)      # columns 0 and D
+    bond = orp_b200.bond_curve(0.05, 1.0, D + 1, D)
+    vals = torch.empty(2 ** m, dtype=torch.float32, device=cuda)
+    sums, _ = orp_b200.payoff_sums(tm, [100.0], [-1], "call", values_out=vals, value_scale=1 / 100.0)
+    res = orp_b200.fit_replication(tm, bond, vals, net="eo", scale=100.0)
+    S = tm.t().cpu().numpy()
+    ref = ofit.backward_replication(S, bond, opaths.payoff(S[:, -1], 100.0, "call") / 100.0, net="eo", scale=100.0,
+                                    batch_size=None)
+    bs = opaths.black_scholes_call(100, 100, 1, .05, .2)
+    mc = np.exp(-0.05) * float(sums[0]) / 2 ** m
+    assert abs(mc - bs) < 5e-3
+    assert abs(res["V0"] / ref["V0"] - 1) < 2e-2, (res["V0"], ref["V0"])
+    assert abs(res["phi0"] - ref["phi0"]) < 2e-2 and abs(res["psi0"] - ref["psi0"]) < 2e-2
+    assert abs(res["V0"] * 100.0 - bs) < 0.15 * bs            # the method's own accuracy (reference: +9 % on EO)
+    assert res["steps"][0]["epochs_run"] == ref["history"][0]["epochs_run"] or abs(
+        res["steps"][0]["epochs_run"] - ref["history"][0]["epochs_run"]) <= 10
+
+
+def test_backward_replication_multistep_and_second_model(cuda):
+    """12 monthly steps, 2^14 paths: EO net vs the oracle; RP net with the pinball second model runs and
+    returns finite hedge weights summing to about the discounted value."""
+    import orp_b200
+    p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 12)
+    m, D = 14, 12
+    tm = orp_b200.simulate_paths("gbm_log", p, m=m, steps=D, time_major=True)
+    bond = orp_b200.bond_curve(0.05, 1.0, D + 1)
+    vals = torch.empty(2 ** m, dtype=torch.float32, device=cuda)
+    orp_b200.payoff_sums(tm, [100.0], [-1], "call", values_out=vals, value_scale=1 / 100.0)
+    res = orp_b200.fit_replication(tm, bond, vals, net="eo", scale=100.0)
+    S = tm.t().cpu().numpy()
+    ref = ofit.backward_replication(S, bond, opaths.payoff(S[:, -1], 100.0, "call") / 100.0, net="eo", scale=100.0,
+                                    batch_size=None)
+    assert len(res["steps"]) == D
+    assert abs(res["V0"] / ref["V0"] - 1) < 5e-2, (res["V0"], ref["V0"])
+    res2 = orp_b200.fit_replication(tm, bond, vals, net="rp", scale=100.0, out_bias=[0.5, 0.5], second_model=True,
+                                    epochs_first=60, epochs_next=10)
+    assert np.isfinite([res2["V0"], res2["phi0"], res2["psi0"]]).all()
+    assert abs(res2["phi0"] * 1.0 + res2["psi0"] * bond[0] / 100.0 - res2["V0"]) < 0.05
