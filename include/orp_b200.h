@@ -32,7 +32,8 @@ extern "C" {
 
 #define ORP_SOBOL_BITS 30      /* scipy default, scipy/stats/_qmc.py:1780-1781 */
 #define ORP_SOBOL_MAXDIM 21201 /* scipy/stats/_sobol.pyi */
-#define ORP_SV_STRIDE 32       /* packed row: 30 direction numbers, word 30 = 0, word 31 = shift */
+#define ORP_SV_WORDS 32        /* packed engine: words 0..29 direction numbers, word 30 = 0, word 31 = shift */
+#define ORP_SV_DPAD(d) (((d) + 31) & ~31)   /* dimensions padded to a multiple of 32 */
 
 int orp_version(void);
 const char* orp_last_error(void);
@@ -51,8 +52,10 @@ int orp_sobol_direction_numbers(const int64_t* poly, const int64_t* vinit, int d
 int orp_sobol_scramble(int d, int bits, const uint32_t* v, const uint32_t* shift_bits, const uint32_t* ltm_bits,
                        uint32_t* sv_out, uint32_t* shift_out);
 
-/* Device-friendly packing (no reference counterpart; derived data): sv32_out[d][32] and the per-lane
- * Gray-code table tlane_out[d][32][2] used by the warp decomposition of the skip-ahead. */
+/* Device-friendly packing (no reference counterpart; derived data): WORD-MAJOR sv32_out[32][ORP_SV_DPAD(d)]
+ * (word b of dimension k at sv32_out[b * dpad + k], so 32 lanes working on 32 consecutive dimensions read one
+ * 128-byte line) and the per-lane Gray-code table tlane_out[d][32][2] used by the warp decomposition of the
+ * skip-ahead. */
 int orp_sobol_pack(int d, int bits, const uint32_t* sv, const uint32_t* shift, uint32_t* sv32_out, uint32_t* tlane_out);
 
 /* ---------------------------------------------------------------- a-2  Sobol points (device) */
@@ -79,7 +82,7 @@ typedef struct orp_path_params {
     int32_t n_steps;     /* D; the engines have d = D + 1 dimensions, step t uses dimension t, dimension 0 unused */
     int32_t keep_every;  /* the reference's `reduction` (Replicating_Portfolio.py:92-93): column t is stored iff t % keep_every == 0 */
     int32_t out_dtype;   /* ORP_F64 / ORP_F32 (arithmetic is fp64 either way) */
-    int32_t reserved;
+    int32_t sobol_dim;   /* d of the engines (the reference's n_time_steps); 0 means n_steps + 1 */
     double s0;           /* Y / S0 */
     double mu;           /* drift: mu (Replicating_Portfolio.py:65, :287) or r (European Options.ipynb cell 6) */
     double sigma;        /* GBM volatility */
@@ -160,8 +163,12 @@ int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const double* d_
 
 /* Stage 2: Adam step (Keras formula, eps 1e-7), epoch loss, LearningRateScheduler (Replicating_Portfolio.py:128-136)
  * and EarlyStopping(monitor='loss', restore_best_weights=True) bookkeeping (:174, :206), all on the device so the
- * host can enqueue epochs without synchronising.  d_state: ORP_FIT_STATE_DOUBLES doubles, layout in orp_fit.cu. */
-int orp_fit_update(int net, float* d_params, double* d_state, const double* d_gsum, void* stream);
+ * host can enqueue epochs without synchronising.  d_state: ORP_FIT_STATE_DOUBLES doubles, layout in orp_fit.cu.
+ * An epoch may be split into several batches (one grad + update pair each, as Keras does with batch_size):
+ * flags bit 0 = first batch of the epoch, bit 1 = last batch (the epoch-end callbacks run then). */
+#define ORP_FIT_EPOCH_FIRST 1
+#define ORP_FIT_EPOCH_LAST 2
+int orp_fit_update(int net, float* d_params, double* d_state, const double* d_gsum, int flags, void* stream);
 
 /* Starts a Model.fit call: resets the early-stopping state, keeps weights and Adam moments (they persist across
  * time steps, Replicating_Portfolio.py:203-211).  use_schedule = 1 for the first fit. */

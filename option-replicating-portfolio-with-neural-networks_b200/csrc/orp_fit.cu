@@ -14,7 +14,7 @@ namespace orp {
 // ---- state layout (indices into the double array) ------------------------------------------------
 enum {
     ST_LR = 0, ST_ADAM_T, ST_EPOCH, ST_EPOCHS, ST_PATIENCE, ST_USE_SCHED, ST_WAIT, ST_BEST, ST_STOP,
-    ST_STOPPED_EARLY, ST_LAST_LOSS, ST_EPOCHS_RUN, ST_HAVE_BEST, ST_TOTAL_EPOCHS,
+    ST_STOPPED_EARLY, ST_LAST_LOSS, ST_EPOCHS_RUN, ST_HAVE_BEST, ST_TOTAL_EPOCHS, ST_LOSS_ACC, ST_COUNT_ACC,
     ST_ADAM_M = 16, ST_ADAM_V = ST_ADAM_M + ORP_FIT_MAX_PARAMS, ST_BEST_W = ST_ADAM_V + ORP_FIT_MAX_PARAMS,
     ST_END = ST_BEST_W + ORP_FIT_MAX_PARAMS
 };
@@ -190,15 +190,19 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
     block_reduce_to<N::P>(g, loss, n, partials + (size_t)blockIdx.x * kGsum);
 }
 
-// fixed-order sum of the per-block partials
-__global__ void fit_reduce_kernel(const double* __restrict__ partials, int n_blocks, const double* __restrict__ state,
-                                  double* __restrict__ gsum) {
+// Fixed-order sum of the per-block partials: lane l adds blocks l, l+32, ... in increasing order, then a
+// shuffle tree combines the 32 lane sums — the same association on every launch, whichever block finished last.
+__global__ void __launch_bounds__(256) fit_reduce_kernel(const double* __restrict__ partials, int n_blocks,
+                                                         const double* __restrict__ state, double* __restrict__ gsum) {
     if (state[ST_STOP] != 0.0) return;
-    const int k = threadIdx.x;
-    if (k >= kGsum) return;
-    double t = 0.0;
-    for (int b = 0; b < n_blocks; ++b) t += partials[(size_t)b * kGsum + k];
-    gsum[k] = t;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int k = warp; k < kGsum; k += 8) {
+        double t = 0.0;
+        for (int b = lane; b < n_blocks; b += 32) t += partials[(size_t)b * kGsum + k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+        if (lane == 0) gsum[k] = t;
+    }
 }
 
 __device__ __forceinline__ double schedule_lr(int epoch, double lr) {      // Replicating_Portfolio.py:128-136
@@ -239,13 +243,15 @@ __device__ void epoch_end(int P, const float* __restrict__ params, double* __res
     if (epoch >= (int)state[ST_EPOCHS]) state[ST_STOP] = 1.0;
 }
 
+// One optimiser step.  flags bit 0: first batch of the epoch (LearningRateScheduler.on_epoch_begin),
+// bit 1: last batch (epoch loss = sample-weighted mean of the batch losses, then the callbacks).
 __global__ void fit_update_kernel(int P, float* __restrict__ params, double* __restrict__ state,
-                                  const double* __restrict__ gsum) {
+                                  const double* __restrict__ gsum, int flags) {
     if (state[ST_STOP] != 0.0) return;
     __shared__ float s_lr_t;
     if (threadIdx.x == 0) {
         double lr = state[ST_LR];
-        if (state[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)state[ST_EPOCH], lr);     // on_epoch_begin
+        if ((flags & 1) && state[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)state[ST_EPOCH], lr);
         state[ST_LR] = lr;
         const double t = state[ST_ADAM_T] + 1.0;
         state[ST_ADAM_T] = t;
@@ -255,7 +261,13 @@ __global__ void fit_update_kernel(int P, float* __restrict__ params, double* __r
     const double inv_n = 1.0 / gsum[ORP_FIT_MAX_PARAMS + 1];
     if (threadIdx.x < P) adam_apply(params, state, threadIdx.x, (float)(gsum[threadIdx.x] * inv_n), s_lr_t);
     __syncthreads();
-    if (threadIdx.x == 0) epoch_end(P, params, state, gsum[ORP_FIT_MAX_PARAMS] * inv_n);
+    if (threadIdx.x == 0) {
+        const double loss_acc = ((flags & 1) ? 0.0 : state[ST_LOSS_ACC]) + gsum[ORP_FIT_MAX_PARAMS];
+        const double cnt_acc = ((flags & 1) ? 0.0 : state[ST_COUNT_ACC]) + gsum[ORP_FIT_MAX_PARAMS + 1];
+        state[ST_LOSS_ACC] = loss_acc;
+        state[ST_COUNT_ACC] = cnt_acc;
+        if (flags & 2) epoch_end(P, params, state, loss_acc / cnt_acc);
+    }
 }
 
 __global__ void fit_init_kernel(double* __restrict__ state) {
@@ -473,16 +485,16 @@ extern "C" int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const
     ORP_FIT_DISPATCH(CALL_GRAD);
 #undef CALL_GRAD
     ORP_LAUNCH_CHECK("fit_grad_kernel");
-    fit_reduce_kernel<<<1, 160, 0, st>>>(partials, grid, d_state, d_gsum);
+    fit_reduce_kernel<<<1, 256, 0, st>>>(partials, grid, d_state, d_gsum);
     ORP_LAUNCH_CHECK("fit_reduce_kernel");
     return ORP_OK;
 }
 
-extern "C" int orp_fit_update(int net, float* d_params, double* d_state, const double* d_gsum, void* stream) {
+extern "C" int orp_fit_update(int net, float* d_params, double* d_state, const double* d_gsum, int flags, void* stream) {
     const int P = orp_fit_n_params(net);
     ORP_REQUIRE(P > 0, "unknown net %d", net);
     ORP_REQUIRE(d_params && d_state && d_gsum, "null pointer");
-    fit_update_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(P, d_params, d_state, d_gsum);
+    fit_update_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(P, d_params, d_state, d_gsum, flags);
     ORP_LAUNCH_CHECK("fit_update_kernel");
     return ORP_OK;
 }

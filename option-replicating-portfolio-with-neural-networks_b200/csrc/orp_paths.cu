@@ -7,6 +7,8 @@
 #include "orp_common.h"
 #include "orp_device.cuh"
 
+#include <cmath>
+#include <cstdlib>
 #include <utility>
 #include <vector>
 
@@ -23,7 +25,7 @@ __global__ void __launch_bounds__(256) ndtri_u32_kernel(const uint32_t* __restri
     load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
     __syncthreads();
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
-        z[i] = ndtri_bits(x[i], s_tab);
+        z[i] = ndtri_bits(x[i], (uint32_t)__cvta_generic_to_shared(s_tab));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -47,7 +49,7 @@ sobol_points_kernel(const uint32_t* __restrict__ sv32, const uint2* __restrict__
         const bool ok0 = i0 >= start && i0 < end, ok1 = i1 >= start && i1 < end;
         for (int t0 = 0; t0 < d; t0 += 32) {
             const int my_dim = t0 + lane;
-            const uint32_t bl = my_dim < d ? warp_base(sv32, my_dim, w) : 0u;
+            const uint32_t bl = my_dim < d ? warp_base(sv32, ORP_SV_DPAD(d), my_dim, w) : 0u;
             const int nc = min(32, d - t0);
             for (int s = 0; s < nc; ++s) {
                 const int t = t0 + s;
@@ -85,7 +87,7 @@ struct PathArgs {
     const uint2* tlane_b;
     void* out;
     uint64_t ld, start, count;
-    int n_steps, keep_every;
+    int n_steps, keep_every, dpad;
     double s0;                // Y / S0
     double c_drift;           // GBM_LOG: (mu - sigma^2/2) dt;  GBM_ARITH: mu dt;  SV: mu
     double c_vol;             // GBM: sigma sqrt(dt);           SV: sqrt(dt)
@@ -125,12 +127,20 @@ __device__ __forceinline__ void advance(const PathArgs& a, double& s_0, double& 
     }
 }
 
-template <int MODEL, typename OutT>
+// FUSED (log-Euler GBM only): the table is transformed so that one Horner chain yields exp(drift + vol z);
+// the state is then the price itself, S_t = S_{t-1} * factor — no exp, no separate normal.
+template <int MODEL, typename OutT, bool FUSED>
 __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a) {
+    static_assert(!FUSED || MODEL == ORP_MODEL_GBM_LOG, "only the log-Euler GBM step fuses into the table");
     extern __shared__ __align__(128) char s_tab[];
     load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
     __syncthreads();
+    if (FUSED) {
+        fuse_gbm_table(s_tab, a.c_drift, a.c_vol, threadIdx.x, blockDim.x);
+        __syncthreads();
+    }
 
+    const uint32_t tab = (uint32_t)__cvta_generic_to_shared(s_tab);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kWarps = kPathThreads / 32;
     const uint64_t end = a.start + a.count;
@@ -143,44 +153,53 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
         const uint64_t w = w_first + tile;
         const uint64_t i0 = w * kWarpPaths + lane, i1 = i0 + 32;
         const bool ok0 = i0 >= a.start && i0 < end, ok1 = i1 >= a.start && i1 < end;
-        const uint64_t j0 = i0 - a.start, j1 = i1 - a.start;
+        const uint64_t j0 = i0 - a.start;
 
         // state: GBM_LOG ln S; GBM_ARITH S; SV ln Y and v
         double s_0, s_1, v_0 = a.v0, v_1 = a.v0;
-        if (kLevel<MODEL>) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
-        if (ok0) store_col<OutT>(a.out, a.ld, 0, j0, a.s0);
-        if (ok1) store_col<OutT>(a.out, a.ld, 0, j1, a.s0);
-        int next_keep = a.keep_every, col = 1;
+        if (kLevel<MODEL> || FUSED) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
+        OutT* __restrict__ optr = reinterpret_cast<OutT*>(a.out) + j0;       // running column pointer (+32 = second path)
+        if (ok0) optr[0] = (OutT)a.s0;
+        if (ok1) optr[32] = (OutT)a.s0;
+        int next_keep = a.keep_every;
 
         for (int t0 = 1; t0 <= D; t0 += 32) {
             const int my_dim = t0 + lane;
             uint32_t bl_a = 0u, bl_b = 0u;
             if (my_dim <= D) {
-                bl_a = warp_base(a.sv32_a, my_dim, w);
-                if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, my_dim, w);
+                bl_a = warp_base(a.sv32_a, a.dpad, my_dim, w);
+                if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, a.dpad, my_dim, w);
             }
             const int nc = min(32, D - t0 + 1);
+            uint2 tl_next = __ldg(a.tlane_a + (size_t)t0 * 32 + lane);
             for (int s = 0; s < nc; ++s) {
                 const int t = t0 + s;
                 const uint32_t base = __shfl_sync(kFull, bl_a, s);
-                const uint2 tl = __ldg(a.tlane_a + (size_t)t * 32 + lane);
-                const double z0 = ndtri_bits(base ^ tl.x, s_tab);
-                const double z1 = ndtri_bits(base ^ tl.y, s_tab);
-                double y0 = 0.0, y1 = 0.0;
-                if (MODEL == ORP_MODEL_SV) {
-                    const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
-                    const uint2 tb = __ldg(a.tlane_b + (size_t)t * 32 + lane);
-                    y0 = ndtri_bits(base_b ^ tb.x, s_tab);
-                    y1 = ndtri_bits(base_b ^ tb.y, s_tab);
+                const uint2 tl = tl_next;                   // fetched one step ahead: its L1 latency hides behind this step
+                tl_next = __ldg(a.tlane_a + (size_t)min(t + 1, D) * 32 + lane);
+                if (FUSED) {
+                    // exp(-inf) = 0 at the exact-zero coordinate, like np.exp of the reference's -inf log-price
+                    s_0 *= table_eval(base ^ tl.x, tab);
+                    s_1 *= table_eval(base ^ tl.y, tab);
+                } else {
+                    const double z0 = ndtri_bits(base ^ tl.x, tab);
+                    const double z1 = ndtri_bits(base ^ tl.y, tab);
+                    double y0 = 0.0, y1 = 0.0;
+                    if (MODEL == ORP_MODEL_SV) {
+                        const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
+                        const uint2 tb = __ldg(a.tlane_b + (size_t)t * 32 + lane);
+                        y0 = ndtri_bits(base_b ^ tb.x, tab);
+                        y1 = ndtri_bits(base_b ^ tb.y, tab);
+                    }
+                    advance<MODEL>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
                 }
-                advance<MODEL>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
                 if (t == next_keep) {
                     double o0 = s_0, o1 = s_1;
-                    if (!kLevel<MODEL>) { o0 = exp(s_0); o1 = exp(s_1); }
-                    if (ok0) store_col<OutT>(a.out, a.ld, col, j0, o0);
-                    if (ok1) store_col<OutT>(a.out, a.ld, col, j1, o1);
+                    if (!kLevel<MODEL> && !FUSED) { o0 = exp(s_0); o1 = exp(s_1); }
+                    optr += a.ld;
+                    if (ok0) optr[0] = (OutT)o0;
+                    if (ok1) optr[32] = (OutT)o1;
                     next_keep += a.keep_every;
-                    ++col;
                 }
             }
         }
@@ -204,6 +223,7 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
     load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
     __syncthreads();
 
+    const uint32_t tab = (uint32_t)__cvta_generic_to_shared(s_tab);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int kWarps = kPathThreads / 32;
     constexpr int NS = MODEL == ORP_MODEL_SV ? 4 : 2;      // stacks: price (2 paths) [+ volatility (2 paths)]
@@ -232,8 +252,8 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
             uint32_t bl_a = 0u, bl_b = 0u;
             if (o0 + lane < D) {
                 const int my_dim = ops[o0 + lane].dim;
-                bl_a = warp_base(a.sv32_a, my_dim, w);
-                if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, my_dim, w);
+                bl_a = warp_base(a.sv32_a, a.dpad, my_dim, w);
+                if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, a.dpad, my_dim, w);
             }
             const int nc = min(32, D - o0);
             for (int s = 0; s < nc; ++s) {
@@ -242,14 +262,14 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
                 {
                     const uint32_t base = __shfl_sync(kFull, bl_a, s);
                     const uint2 tl = __ldg(a.tlane_a + (size_t)op.dim * 32 + lane);
-                    zz[0] = ndtri_bits(base ^ tl.x, s_tab);
-                    zz[1] = ndtri_bits(base ^ tl.y, s_tab);
+                    zz[0] = ndtri_bits(base ^ tl.x, tab);
+                    zz[1] = ndtri_bits(base ^ tl.y, tab);
                 }
                 if (MODEL == ORP_MODEL_SV) {
                     const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
                     const uint2 tb = __ldg(a.tlane_b + (size_t)op.dim * 32 + lane);
-                    zz[NS - 2] = ndtri_bits(base_b ^ tb.x, s_tab);
-                    zz[NS - 1] = ndtri_bits(base_b ^ tb.y, s_tab);
+                    zz[NS - 2] = ndtri_bits(base_b ^ tb.x, tab);
+                    zz[NS - 1] = ndtri_bits(base_b ^ tb.y, tab);
                 }
                 // W_m = wl W_left + wr W_right + sd z   (left = last emitted node, right = stack top)
 #pragma unroll
@@ -289,14 +309,14 @@ static int set_table_smem(K kernel) {
     return ORP_OK;
 }
 
-template <int MODEL, typename OutT>
+template <int MODEL, typename OutT, bool FUSED = false>
 static int launch_paths(const PathArgs& a, cudaStream_t st) {
-    int rc = set_table_smem(paths_kernel<MODEL, OutT>);
+    int rc = set_table_smem(paths_kernel<MODEL, OutT, FUSED>);
     if (rc) return rc;
     const uint64_t n_tiles = (a.start + a.count - 1) / kWarpPaths - a.start / kWarpPaths + 1;
     const uint64_t want = (n_tiles + 31) / 32;
     const int grid = (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
-    paths_kernel<MODEL, OutT><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a);
+    paths_kernel<MODEL, OutT, FUSED><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a);
     ORP_LAUNCH_CHECK("paths_kernel");
     return ORP_OK;
 }
@@ -418,6 +438,9 @@ extern "C" int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const
     a.sv32_b = d_sv32_b; a.tlane_b = reinterpret_cast<const uint2*>(d_tlane_b);
     a.out = d_out; a.ld = ld; a.start = start; a.count = count;
     a.n_steps = p->n_steps; a.keep_every = p->keep_every;
+    const int sobol_dim = p->sobol_dim > 0 ? p->sobol_dim : p->n_steps + 1;
+    ORP_REQUIRE(sobol_dim >= p->n_steps + 1 && sobol_dim <= ORP_SOBOL_MAXDIM, "sobol_dim must be in [n_steps + 1, %d]", ORP_SOBOL_MAXDIM);
+    a.dpad = ORP_SV_DPAD(sobol_dim);
     a.s0 = p->s0; a.dt = p->dt; a.v0 = p->v0; a.a = p->a; a.b = p->b; a.c = p->c;
     const double sqdt = sqrt(p->dt);
     switch (p->model) {
@@ -438,7 +461,11 @@ extern "C" int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const
     cudaStream_t st = (cudaStream_t)stream;
     const bool f32 = p->out_dtype == ORP_F32;
     switch (p->model) {
-        case ORP_MODEL_GBM_LOG:   return f32 ? launch_paths<ORP_MODEL_GBM_LOG, float>(a, st)   : launch_paths<ORP_MODEL_GBM_LOG, double>(a, st);
+        case ORP_MODEL_GBM_LOG:
+            // |vol| < 1/4 per step keeps the table transform's truncation below 1e-15; larger steps take the generic path
+            if (fabs(a.c_vol) < 0.25 && fabs(a.c_drift) < 1.0 && !getenv("ORP_B200_NO_FUSE"))
+                return f32 ? launch_paths<ORP_MODEL_GBM_LOG, float, true>(a, st) : launch_paths<ORP_MODEL_GBM_LOG, double, true>(a, st);
+            return f32 ? launch_paths<ORP_MODEL_GBM_LOG, float>(a, st) : launch_paths<ORP_MODEL_GBM_LOG, double>(a, st);
         case ORP_MODEL_GBM_ARITH: return f32 ? launch_paths<ORP_MODEL_GBM_ARITH, float>(a, st) : launch_paths<ORP_MODEL_GBM_ARITH, double>(a, st);
         case ORP_MODEL_LINEAR:    return f32 ? launch_paths<ORP_MODEL_LINEAR, float>(a, st)    : launch_paths<ORP_MODEL_LINEAR, double>(a, st);
         default:                  return f32 ? launch_paths<ORP_MODEL_SV, float>(a, st)        : launch_paths<ORP_MODEL_SV, double>(a, st);

@@ -91,11 +91,12 @@ extern "C" int orp_sobol_pack(int d, int bits, const uint32_t* sv, const uint32_
     ORP_REQUIRE(sv && shift && sv32_out && tlane_out, "null pointer");
     ORP_REQUIRE(d >= 1 && d <= ORP_SOBOL_MAXDIM, "Maximum supported dimensionality is %d.", ORP_SOBOL_MAXDIM);
     ORP_REQUIRE(bits == ORP_SOBOL_BITS, "the device path is built for bits = %d (SciPy's default)", ORP_SOBOL_BITS);
+    const size_t dpad = (size_t)ORP_SV_DPAD(d);
+    for (size_t i = 0; i < dpad * ORP_SV_WORDS; ++i) sv32_out[i] = 0u;
     for (int k = 0; k < d; ++k) {
-        uint32_t* row = sv32_out + (size_t)k * ORP_SV_STRIDE;
         const uint32_t* s = sv + (size_t)k * bits;
-        for (int b = 0; b < ORP_SV_STRIDE; ++b) row[b] = b < bits ? s[b] : 0u;
-        row[31] = shift[k];
+        for (int b = 0; b < bits; ++b) sv32_out[(size_t)b * dpad + k] = s[b];
+        sv32_out[(size_t)31 * dpad + k] = shift[k];
         // Path index i = 64 w + 32 p + l  =>  gray bits 0..3 = l_b ^ l_{b+1}, bit 4 = l_4 ^ p, bit 5 = p ^ w_0.
         for (int l = 0; l < 32; ++l) {
             uint32_t t = 0;

@@ -35,7 +35,7 @@ ST_BEST_W = ST_ADAM_V + FIT_MAX_PARAMS
 
 class PathParams(C.Structure):
     _fields_ = [("model", C.c_int32), ("ordering", C.c_int32), ("n_steps", C.c_int32), ("keep_every", C.c_int32),
-                ("out_dtype", C.c_int32), ("reserved", C.c_int32),
+                ("out_dtype", C.c_int32), ("sobol_dim", C.c_int32),
                 ("s0", C.c_double), ("mu", C.c_double), ("sigma", C.c_double), ("dt", C.c_double),
                 ("v0", C.c_double), ("a", C.c_double), ("b", C.c_double), ("c", C.c_double)]
 
@@ -66,7 +66,7 @@ PROTOTYPES = {
     "orp_fit_n_params": (C.c_int, [_i32]),
     "orp_fit_scratch_bytes": (C.c_uint64, []),
     "orp_fit_grad": (C.c_int, [C.POINTER(FitBatch), _vp, _vp, _vp, _vp, _vp]),
-    "orp_fit_update": (C.c_int, [_i32, _vp, _vp, _vp, _vp]),
+    "orp_fit_update": (C.c_int, [_i32, _vp, _vp, _vp, _i32, _vp]),
     "orp_fit_begin": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
     "orp_fit_init": (C.c_int, [_vp, _vp]),
     "orp_fit_end": (C.c_int, [_i32, _vp, _vp, _vp]),

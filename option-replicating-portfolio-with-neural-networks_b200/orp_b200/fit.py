@@ -85,29 +85,58 @@ class ReplicationNet:
         b.d_feat1, b.d_feat2, b.d_target = _lib.ptr(feat1) or None, _lib.ptr(feat2) or None, _lib.ptr(target) or None
         b.inv_scale, b.bond_t, b.bond_t1 = float(inv_scale), float(bond_t), float(bond_t1)
         b._keep = (s_t, s_t1, target, feat1, feat2)          # keep the tensors alive
+        b._esz = s_t.element_size()
         return b
 
+    @staticmethod
+    def split(b, steps_per_epoch: int):
+        """The batch cut into ``steps_per_epoch`` contiguous index ranges (Keras' ``batch_size`` =
+        ``count / steps_per_epoch``).  Contiguous blocks of a Sobol sequence are themselves well stratified,
+        so no shuffle is needed; on several GPUs batch ``k`` is the union of every rank's ``k``-th range."""
+        n = int(b.count)
+        k = max(1, min(int(steps_per_epoch), n))
+        if k == 1:
+            return [b]
+        per = -(-n // k)
+        out = []
+        for off in range(0, n, per):
+            c = _lib.FitBatch()
+            C.memmove(C.byref(c), C.byref(b), C.sizeof(_lib.FitBatch))
+            c.count = min(per, n - off)
+            c.d_s_t, c.d_s_t1 = b.d_s_t + off * b._esz, b.d_s_t1 + off * b._esz
+            c.d_target = b.d_target + off * 4 if b.d_target else None
+            c.d_feat1 = b.d_feat1 + off * 4 if b.d_feat1 else None
+            c.d_feat2 = b.d_feat2 + off * 4 if b.d_feat2 else None
+            c._keep = b._keep
+            out.append(c)
+        return out
+
     def fit(self, batch, opt: Optimizer, epochs: int, patience: int, use_schedule: bool, mode: str = "scaled",
-            batch_size: int = 512, shuffle_seed: int = 0, check_every: int = 16):
-        """One ``Model.fit`` (``Replicating_Portfolio.py:211``).  Returns ``dict(epochs_run, loss,
-        stopped_early, lr)``."""
+            batch_size: int = 512, shuffle_seed: int = 0, check_every: int = 16, steps_per_epoch: int = 1):
+        """One ``Model.fit`` (``Replicating_Portfolio.py:211``).  ``steps_per_epoch`` (scaled mode): optimiser
+        steps per pass over the paths.  Returns ``dict(epochs_run, loss, stopped_early, lr)``."""
         torch = _lib.require_cuda()
         L = _lib.lib()
         netc = _lib.NET[self.net]
         with torch.cuda.device(self.device):
             st = _lib.stream_ptr()
             _lib.check(L.orp_fit_begin(_lib.ptr(opt.state), int(epochs), int(patience), int(bool(use_schedule)), st))
+            parts = self.split(batch, steps_per_epoch) if mode == "scaled" else [batch]
+            dist_on = is_distributed(self.group)
             done = 0
             while done < epochs:
                 n = min(check_every, epochs - done)
                 for e in range(n):
                     if mode == "scaled":
-                        _lib.check(L.orp_fit_grad(C.byref(batch), _lib.ptr(self.params), _lib.ptr(opt.state),
-                                                  _lib.ptr(self.gsum), _lib.ptr(self.scratch), st))
-                        if is_distributed(self.group):
-                            allreduce_sum_(self.gsum, self.group)
-                        _lib.check(L.orp_fit_update(netc, _lib.ptr(self.params), _lib.ptr(opt.state), _lib.ptr(self.gsum), st))
-                        self.launches += 3
+                        for k, part in enumerate(parts):
+                            _lib.check(L.orp_fit_grad(C.byref(part), _lib.ptr(self.params), _lib.ptr(opt.state),
+                                                      _lib.ptr(self.gsum), _lib.ptr(self.scratch), st))
+                            if dist_on:
+                                allreduce_sum_(self.gsum, self.group)
+                            flags = (1 if k == 0 else 0) | (2 if k == len(parts) - 1 else 0)
+                            _lib.check(L.orp_fit_update(netc, _lib.ptr(self.params), _lib.ptr(opt.state),
+                                                        _lib.ptr(self.gsum), flags, st))
+                        self.launches += 3 * len(parts)
                     elif mode == "keras":
                         if is_distributed(self.group):
                             raise ValueError("mode='keras' is serial by definition: replicas only, no sharding")
@@ -141,13 +170,16 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
                     out_bias=None, init_seed: int = 1234, total_paths: int | None = None, group=None,
                     epochs_first: int = 500, epochs_next: int = 100, patience_first: int = 50, patience_next: int = 7,
                     batch_size: int = 512, shuffle_seed: int = 0, features=None, second_model: bool = False,
-                    cost_of_capital: float = 0.1, check_every: int = 16, verbose: bool = False, on_step=None):
+                    cost_of_capital: float = 0.1, check_every: int = 16, verbose: bool = False, on_step=None,
+                    steps_per_epoch: int = 8):
     """Backward replication over all kept columns.
 
     ``paths_tm``: TIME-MAJOR ``(n_cols, count)`` CUDA tensor of this rank's paths; ``bond``: ``n_cols`` bond
     prices; ``terminal_values``: fp32 ``(count,)`` CUDA tensor in network units (EO: ``payoff / S0``).
     ``scale`` = ``ADJUSTMENT_FACTOR`` dividing prices (EO cell 13: ``S0``).  ``features(t_i)`` returns the two
-    extra fp32 inputs of the ``'rp'`` net ``(N_t/N, lambda_t)`` or ``None``.  ``second_model=True`` adds the
+    extra fp32 inputs of the ``'rp'`` net ``(N_t/N, lambda_t)`` or ``None``.
+    ``steps_per_epoch`` (scaled mode): Adam steps per pass over the paths; the default 8 is the reference
+    notebook's own ratio (4096 paths / batch 512, ``European Options.ipynb`` cell 13), kept at every scale.  ``second_model=True`` adds the
     pinball-loss fit of the SAME weights and the blend ``values = g + cost_of_capital (h - g)``
     (``Replicating_Portfolio.py:217-221``; the reference's model2 aliases model1's layers).
 
@@ -180,7 +212,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
         b = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="mse", **common)
         h = model.fit(b, opt1, epochs_first if first else epochs_next, patience_first if first else patience_next,
                       use_schedule=first, mode=mode, batch_size=batch_size,
-                      shuffle_seed=shuffle_seed * 4096 + 2 * t_i, check_every=check_every)
+                      shuffle_seed=shuffle_seed * 4096 + 2 * t_i, check_every=check_every, steps_per_epoch=steps_per_epoch)
         sums = model.predict(b, v_cur)
         rec = dict(t_i=t_i, epochs_run=h["epochs_run"], loss=h["loss"], stopped_early=h["stopped_early"],
                    mean_V=sums[0] / total, phi=sums[1] / total, psi=sums[2] / total, mae=sums[3] / total)
@@ -188,7 +220,8 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
             b2 = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="pinball", **common)
             h2 = model.fit(b2, opt2, epochs_first if first else epochs_next, patience_first if first else patience_next,
                            use_schedule=first, mode=mode, batch_size=batch_size,
-                           shuffle_seed=shuffle_seed * 4096 + 2 * t_i + 1, check_every=check_every)
+                           shuffle_seed=shuffle_seed * 4096 + 2 * t_i + 1, check_every=check_every,
+                           steps_per_epoch=steps_per_epoch)
             sums2 = model.predict(b2, h_buf)
             v_cur.add_(h_buf - v_cur, alpha=cost_of_capital)     # values = g + cc (h - g)
             # get_phi_psi_VaR reads the shared 'Phi_Psi' layer after BOTH fits (Replicating_Portfolio.py:104-115)

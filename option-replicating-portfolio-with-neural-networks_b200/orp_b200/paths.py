@@ -101,6 +101,7 @@ def simulate_paths(model: str, params: dict, m: int | None = None, steps: int | 
     p = _lib.PathParams()
     p.model, p.ordering, p.n_steps, p.keep_every = _lib.MODEL[model], _lib.ORDER[ordering], steps, keep_every
     p.out_dtype = _DTYPES[dtype]
+    p.sobol_dim = d
     p.s0 = float(params.get("S0", params.get("Y", 1.0)))
     p.mu = float(params.get("mu", params.get("r", 0.0)))
     p.sigma = float(params.get("sigma", 0.0))

@@ -52,7 +52,7 @@ class SobolEngine:
                                             _lib.ptr(self.sv), _lib.ptr(self.shift)))
         else:
             self.sv, self.shift = v, np.zeros(d, dtype=np.uint32)
-        self.sv32 = np.zeros((d, 32), dtype=np.uint32)
+        self.sv32 = np.zeros((32, (d + 31) & ~31), dtype=np.uint32)     # word-major, dimensions padded to 32
         self.tlane = np.zeros((d, 32, 2), dtype=np.uint32)
         _lib.check(L.orp_sobol_pack(d, BITS, _lib.ptr(self.sv), _lib.ptr(self.shift),
                                     _lib.ptr(self.sv32), _lib.ptr(self.tlane)))

@@ -206,7 +206,7 @@ def backward_replication(S_cols: np.ndarray, B_cols: np.ndarray, terminal_value:
         out_bias = float(terminal_value.mean())
     params = torch.from_numpy(init_params(net, init_seed, out_bias).copy())
     opt = AdamState(params.numel())
-    rng = np.random.default_rng(shuffle_seed)
+    rng = np.random.default_rng(shuffle_seed) if shuffle_seed is not None else None     # None: index order, no shuffle
     values = np.empty((n_paths, n))
     values[:, -1] = terminal_value
     hist, phi0, psi0 = [], None, None

@@ -44,7 +44,8 @@ def test_host_setup_bit_exact(d, seed):
     e = SobolEngine(d, seed)
     ref = osobol.scipy_engine(d, seed)
     assert np.array_equal(e.sv, ref._sv) and np.array_equal(e.shift, ref._shift)
-    assert np.array_equal(e.sv32[:, :30], ref._sv) and np.array_equal(e.sv32[:, 31], ref._shift)
+    assert np.array_equal(e.sv32[:30, :d].T, ref._sv) and np.array_equal(e.sv32[31, :d], ref._shift)
+    assert not e.sv32[30].any() and not e.sv32[:, d:].any()
     # lane table against the closed form: index i = 32 p + l of warp tile 0 (shift and base removed)
     x = osobol.points_u32(ref._sv, np.zeros(d, dtype=np.uint32), 0, 64)          # (64, d)
     assert np.array_equal(e.tlane[:, :, 0], x[:32].T) and np.array_equal(e.tlane[:, :, 1], x[32:].T)
