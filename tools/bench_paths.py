@@ -10,7 +10,7 @@ import torch  # noqa: E402
 import orp_b200  # noqa: E402
 
 m = int(sys.argv[1]) if len(sys.argv) > 1 else 24
-D = 252
+D = int(sys.argv[2]) if len(sys.argv) > 2 else 252
 cases = [("gbm_log", "float64", "incremental", 1), ("gbm_log", "float32", "incremental", 1), ("gbm_arith", "float64", "incremental", 1),
          ("sv", "float64", "incremental", 1), ("gbm_log", "float64", "bridge", 1), ("gbm_log", "float64", "incremental", 21)]
 P = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / D, s0=0.16679, a=0.0033281299103885727, b=0.1562947229160206, c=0.01583113545983743)
