@@ -34,79 +34,210 @@ static_assert(Net<ORP_NET_EO>::P == 97 && Net<ORP_NET_RP>::P == 122, "parameter 
 __device__ __forceinline__ float lrelu(float x) { return fmaxf(x, kLeaky * x); }
 __device__ __forceinline__ float dlrelu(float pre) { return pre > 0.f ? 1.f : kLeaky; }
 
-// Forward pass; returns V, optionally phi/psi and the activations needed by the backward pass.
+// ---- packed fp32 pairs ----------------------------------------------------------------------------
+// Blackwell issues a 3-register FFMA every other cycle per scheduler; the packed FFMA2 (PTX fma.rn.f32x2)
+// does two fp32 FMAs in the same slot.  One sample per thread, so the pairs run along the OUTPUT index of
+// each layer: (j, j+1) share the scalar input, which FFMA2 takes as a broadcast operand.  Per-lane results
+// are the IEEE fp32 FMA results of the scalar code.
+typedef float2 f2;
+__device__ __forceinline__ unsigned long long pk(f2 v) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(v.x), "f"(v.y));
+    return r;
+}
+__device__ __forceinline__ f2 upk(unsigned long long r) {
+    f2 v;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(v.x), "=f"(v.y) : "l"(r));
+    return v;
+}
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)), "l"(pk(c)));
+    return upk(d);
+}
+__device__ __forceinline__ f2 fma2s(float a, f2 b, f2 c) { return fma2(make_float2(a, a), b, c); }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+    unsigned long long d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)));
+    return upk(d);
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(pk(a)), "l"(pk(b)));
+    return upk(d);
+}
+// Weight pairs k, k+1 (k even) of the shared-memory image, as one LDS.128.  `volatile` keeps the compiler from
+// hoisting the ~160 loop-invariant weights into registers (which spills the gradient accumulators): they are
+// re-read every sample as broadcast loads, which is what shared memory is good at.
+struct f2x2 { f2 a, b; };
+__device__ __forceinline__ f2x2 ldw(uint32_t s_w, int pair) {
+    f2x2 r;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.a.x), "=f"(r.a.y), "=f"(r.b.x), "=f"(r.b.y) : "r"(s_w + 8u * (uint32_t)pair));
+    return r;
+}
+__device__ __forceinline__ float ldw1(uint32_t s_w, int k) {
+    float r;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(r) : "r"(s_w + 4u * (uint32_t)k));
+    return r;
+}
+__device__ __forceinline__ f2 lrelu2(f2 v) {
+    const f2 s = mul2(make_float2(kLeaky, kLeaky), v);
+    return make_float2(fmaxf(v.x, s.x), fmaxf(v.y, s.y));
+}
+__device__ __forceinline__ f2 dlrelu2(f2 pre) { return make_float2(dlrelu(pre.x), dlrelu(pre.y)); }
+__device__ __forceinline__ float elem(const f2 (&v)[kH / 2], int i) { return (i & 1) ? v[i >> 1].y : v[i >> 1].x; }
+
+// Shared-memory image of the weights: the parameter vector (every block of it starts at an even offset, so
+// it is also an array of pairs) followed by W2 transposed, which the backward pass reads pairwise over the
+// INPUT index.
+constexpr int kW2T = ORP_FIT_MAX_PARAMS;                 // float offset of W2^T[j][i]
+constexpr int kSmemW = ORP_FIT_MAX_PARAMS + kH * kH;
+
 template <int NET>
-__device__ __forceinline__ float net_forward(const float* __restrict__ w, const float (&x)[Net<NET>::IN], float p0, float p1,
-                                             float (&pre1)[kH], float (&h1)[kH], float (&pre2)[kH], float (&h2)[kH],
-                                             float& phi, float& psi) {
+__device__ __forceinline__ void load_weights(float* __restrict__ s_w, const float* __restrict__ params, int tid, int nthreads) {
     using N = Net<NET>;
+    for (int k = tid; k < N::P; k += nthreads) s_w[k] = params[k];
+    for (int k = tid; k < kH * kH; k += nthreads) s_w[kW2T + (k & 7) * kH + (k >> 3)] = params[N::W2 + k];   // k = i*8+j -> [j][i]
+}
+
+template <int NET> struct Acts {
+    f2 pre1[kH / 2], h1[kH / 2], pre2[kH / 2], h2[kH / 2];
+};
+
+// Forward pass; returns V, phi/psi and the activations needed by the backward pass.  `w` is the shared-space
+// address of the weight image.
+template <int NET>
+__device__ __forceinline__ float net_forward(uint32_t w, const float (&x)[Net<NET>::IN], float p0, float p1,
+                                             Acts<NET>& a, float& phi, float& psi) {
+    using N = Net<NET>;
+    static_assert(N::W1 % 4 == 0 && N::B1 % 4 == 0 && N::W2 % 4 == 0 && N::B2 % 4 == 0 && N::W3 % 4 == 0 && N::B3 % 2 == 0,
+                  "parameter blocks must be 16-byte aligned for the paired loads");
 #pragma unroll
-    for (int j = 0; j < kH; ++j) {
-        float acc = w[N::B1 + j];
+    for (int q = 0; q < kH / 4; ++q) { const f2x2 b = ldw(w, N::B1 / 2 + 2 * q); a.pre1[2 * q] = b.a; a.pre1[2 * q + 1] = b.b; }
 #pragma unroll
-        for (int i = 0; i < N::IN; ++i) acc = fmaf(x[i], w[N::W1 + i * kH + j], acc);
-        pre1[j] = acc; h1[j] = lrelu(acc);
+    for (int i = 0; i < N::IN; ++i)
+#pragma unroll
+        for (int q = 0; q < kH / 4; ++q) {
+            const f2x2 c = ldw(w, (N::W1 + i * kH) / 2 + 2 * q);
+            a.pre1[2 * q] = fma2s(x[i], c.a, a.pre1[2 * q]);
+            a.pre1[2 * q + 1] = fma2s(x[i], c.b, a.pre1[2 * q + 1]);
+        }
+#pragma unroll
+    for (int q = 0; q < kH / 4; ++q) { const f2x2 b = ldw(w, N::B2 / 2 + 2 * q); a.pre2[2 * q] = b.a; a.pre2[2 * q + 1] = b.b; }
+#pragma unroll
+    for (int jp = 0; jp < kH / 2; ++jp) a.h1[jp] = lrelu2(a.pre1[jp]);
+#pragma unroll
+    for (int i = 0; i < kH; ++i) {
+        const float hi = elem(a.h1, i);
+#pragma unroll
+        for (int q = 0; q < kH / 4; ++q) {
+            const f2x2 c = ldw(w, (N::W2 + i * kH) / 2 + 2 * q);
+            a.pre2[2 * q] = fma2s(hi, c.a, a.pre2[2 * q]);
+            a.pre2[2 * q + 1] = fma2s(hi, c.b, a.pre2[2 * q + 1]);
+        }
     }
 #pragma unroll
-    for (int j = 0; j < kH; ++j) {
-        float acc = w[N::B2 + j];
+    for (int jp = 0; jp < kH / 2; ++jp) a.h2[jp] = lrelu2(a.pre2[jp]);
+    if (NET == ORP_NET_EO) {
+        const f2x2 c0 = ldw(w, N::W3 / 2), c1 = ldw(w, N::W3 / 2 + 2);        // phi = b3 + sum_i h2[i] w3[i], pairs over i
+        f2 s = mul2(a.h2[0], c0.a);
+        s = fma2(a.h2[1], c0.b, s);
+        s = fma2(a.h2[2], c1.a, s);
+        s = fma2(a.h2[3], c1.b, s);
+        phi = ldw1(w, N::B3) + (s.x + s.y);
+        psi = 1.f - phi;
+    } else {
+        f2 o = make_float2(ldw1(w, N::B3), ldw1(w, N::B3 + 1));               // (phi, psi) = b3 + sum_i h2[i] W3[i][0:2]
 #pragma unroll
-        for (int i = 0; i < kH; ++i) acc = fmaf(h1[i], w[N::W2 + i * kH + j], acc);
-        pre2[j] = acc; h2[j] = lrelu(acc);
+        for (int q = 0; q < kH / 2; ++q) {
+            const f2x2 c = ldw(w, N::W3 / 2 + 2 * q);
+            o = fma2s(elem(a.h2, 2 * q), c.a, o);
+            o = fma2s(elem(a.h2, 2 * q + 1), c.b, o);
+        }
+        phi = o.x; psi = o.y;
     }
-    float out[N::OUT];
-#pragma unroll
-    for (int o = 0; o < N::OUT; ++o) {
-        float acc = w[N::B3 + o];
-#pragma unroll
-        for (int i = 0; i < kH; ++i) acc = fmaf(h2[i], w[N::W3 + i * N::OUT + o], acc);
-        out[o] = acc;
-    }
-    phi = out[0];
-    psi = NET == ORP_NET_EO ? 1.f - phi : out[N::OUT - 1];
     return fmaf(phi, p0, psi * p1);
 }
 
-// Backward pass of V = phi p0 + psi p1 for one sample, accumulating into g[P].
+// Gradient accumulators of one thread, as pairs in the order of the parameter vector.
+template <int NET> struct Grads {
+    static_assert(Net<NET>::P % 2 == (NET == ORP_NET_EO ? 1 : 0), "pair layout");
+    f2 v[Net<NET>::P / 2];
+    float last;                                      // EO: the single output bias (P is odd)
+    __device__ __forceinline__ void zero() {
+#pragma unroll
+        for (int k = 0; k < Net<NET>::P / 2; ++k) v[k] = make_float2(0.f, 0.f);
+        last = 0.f;
+    }
+    __device__ __forceinline__ float get(int k) const {      // k is a compile-time constant after unrolling
+        return k == 2 * (Net<NET>::P / 2) ? last : ((k & 1) ? v[k >> 1].y : v[k >> 1].x);
+    }
+};
+
+// Backward pass of V = phi p0 + psi p1 for one sample, accumulating into g.
 template <int NET>
-__device__ __forceinline__ void net_backward(const float* __restrict__ w, const float (&x)[Net<NET>::IN], float p0, float p1,
-                                             float dV, const float (&pre1)[kH], const float (&h1)[kH],
-                                             const float (&pre2)[kH], const float (&h2)[kH], float (&g)[Net<NET>::P]) {
+__device__ __forceinline__ void net_backward(uint32_t w, const float (&x)[Net<NET>::IN], float p0, float p1,
+                                             float dV, const Acts<NET>& a, Grads<NET>& g) {
     using N = Net<NET>;
-    float dout[N::OUT];
-    if (NET == ORP_NET_EO) dout[0] = dV * (p0 - p1);          // psi = 1 - phi
-    else { dout[0] = dV * p0; dout[N::OUT - 1] = dV * p1; }
-    float d2[kH];
+    f2 d2[kH / 2];
+    if (NET == ORP_NET_EO) {
+        const float dphi = dV * (p0 - p1);                                    // psi = 1 - phi
+        const f2 dd = make_float2(dphi, dphi);
 #pragma unroll
-    for (int i = 0; i < kH; ++i) {
-        float acc = 0.f;
-#pragma unroll
-        for (int o = 0; o < N::OUT; ++o) {
-            g[N::W3 + i * N::OUT + o] = fmaf(h2[i], dout[o], g[N::W3 + i * N::OUT + o]);
-            acc = fmaf(dout[o], w[N::W3 + i * N::OUT + o], acc);
+        for (int q = 0; q < kH / 4; ++q) {
+            const f2x2 c = ldw(w, N::W3 / 2 + 2 * q);
+            g.v[N::W3 / 2 + 2 * q] = fma2(dd, a.h2[2 * q], g.v[N::W3 / 2 + 2 * q]);
+            g.v[N::W3 / 2 + 2 * q + 1] = fma2(dd, a.h2[2 * q + 1], g.v[N::W3 / 2 + 2 * q + 1]);
+            d2[2 * q] = mul2(mul2(dd, c.a), dlrelu2(a.pre2[2 * q]));
+            d2[2 * q + 1] = mul2(mul2(dd, c.b), dlrelu2(a.pre2[2 * q + 1]));
         }
-        d2[i] = acc * dlrelu(pre2[i]);
-    }
+        g.last += dphi;
+    } else {
+        const f2 dout = make_float2(dV * p0, dV * p1);
+        float d2s[kH];
 #pragma unroll
-    for (int o = 0; o < N::OUT; ++o) g[N::B3 + o] += dout[o];
-    float d1[kH];
-#pragma unroll
-    for (int i = 0; i < kH; ++i) {
-        float acc = 0.f;
-#pragma unroll
-        for (int j = 0; j < kH; ++j) {
-            g[N::W2 + i * kH + j] = fmaf(h1[i], d2[j], g[N::W2 + i * kH + j]);
-            acc = fmaf(d2[j], w[N::W2 + i * kH + j], acc);
+        for (int q = 0; q < kH / 2; ++q) {
+            const f2x2 c = ldw(w, N::W3 / 2 + 2 * q);
+            g.v[N::W3 / 2 + 2 * q] = fma2s(elem(a.h2, 2 * q), dout, g.v[N::W3 / 2 + 2 * q]);
+            g.v[N::W3 / 2 + 2 * q + 1] = fma2s(elem(a.h2, 2 * q + 1), dout, g.v[N::W3 / 2 + 2 * q + 1]);
+            const f2 t0 = mul2(dout, c.a), t1 = mul2(dout, c.b);
+            d2s[2 * q] = t0.x + t0.y;
+            d2s[2 * q + 1] = t1.x + t1.y;
         }
-        d1[i] = acc * dlrelu(pre1[i]);
+#pragma unroll
+        for (int ip = 0; ip < kH / 2; ++ip) d2[ip] = mul2(make_float2(d2s[2 * ip], d2s[2 * ip + 1]), dlrelu2(a.pre2[ip]));
+        g.v[N::B3 / 2] = add2(g.v[N::B3 / 2], dout);
+    }
+    f2 d1[kH / 2];
+#pragma unroll
+    for (int ip = 0; ip < kH / 2; ++ip) d1[ip] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < kH; ++j) {                                            // d1[i] = sum_j d2[j] W2[i][j], pairs over i
+        const float dj = elem(d2, j);
+#pragma unroll
+        for (int q = 0; q < kH / 4; ++q) {
+            const f2x2 c = ldw(w, (kW2T + j * kH) / 2 + 2 * q);
+            d1[2 * q] = fma2s(dj, c.a, d1[2 * q]);
+            d1[2 * q + 1] = fma2s(dj, c.b, d1[2 * q + 1]);
+        }
     }
 #pragma unroll
-    for (int j = 0; j < kH; ++j) {
-        g[N::B2 + j] += d2[j];
-        g[N::B1 + j] += d1[j];
+    for (int i = 0; i < kH; ++i) {                                            // dW2[i][j] += h1[i] d2[j], pairs over j
+        const float hi = elem(a.h1, i);
 #pragma unroll
-        for (int i = 0; i < N::IN; ++i) g[N::W1 + i * kH + j] = fmaf(x[i], d1[j], g[N::W1 + i * kH + j]);
+        for (int jp = 0; jp < kH / 2; ++jp) g.v[(N::W2 + i * kH) / 2 + jp] = fma2s(hi, d2[jp], g.v[(N::W2 + i * kH) / 2 + jp]);
     }
+#pragma unroll
+    for (int jp = 0; jp < kH / 2; ++jp) {
+        d1[jp] = mul2(d1[jp], dlrelu2(a.pre1[jp]));
+        g.v[N::B2 / 2 + jp] = add2(g.v[N::B2 / 2 + jp], d2[jp]);
+        g.v[N::B1 / 2 + jp] = add2(g.v[N::B1 / 2 + jp], d1[jp]);
+    }
+#pragma unroll
+    for (int i = 0; i < N::IN; ++i)
+#pragma unroll
+        for (int jp = 0; jp < kH / 2; ++jp) g.v[(N::W1 + i * kH) / 2 + jp] = fma2s(x[i], d1[jp], g.v[(N::W1 + i * kH) / 2 + jp]);
 }
 
 // per-sample loss and dLoss/dV (without the 1/N of the batch mean)
@@ -141,13 +272,14 @@ __device__ __forceinline__ void load_sample(const FitArgs& a, uint64_t i, float 
 constexpr int kFitThreads = 256;
 constexpr int kGsum = ORP_FIT_MAX_PARAMS + 2;      // grads, loss sum, count
 
-template <int P>
-__device__ __forceinline__ void block_reduce_to(float (&g)[P], float loss, uint64_t n, double* __restrict__ dst) {
+template <int NET>
+__device__ __forceinline__ void block_reduce_to(const Grads<NET>& g, float loss, uint32_t n, double* __restrict__ dst) {
+    constexpr int P = Net<NET>::P;
     __shared__ float s_red[kFitThreads / 32][P + 2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int k = 0; k < P; ++k) {
-        float v = g[k];
+        float v = g.get(k);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
         if (lane == 0) s_red[warp][k] = v;
@@ -164,30 +296,83 @@ __device__ __forceinline__ void block_reduce_to(float (&g)[P], float loss, uint6
     }
 }
 
+// Raw inputs of one sample, as loaded (conversion to the network's fp32 happens when the sample is used).
+template <int NET, typename T> struct RawSample {
+    T s_t, s_t1;
+    float y, f1, f2;
+};
+
+template <int NET, typename T>
+__device__ __forceinline__ void load_raw(const FitArgs& a, uint64_t i, RawSample<NET, T>& r) {
+    r.s_t = reinterpret_cast<const T*>(a.s_t)[i];
+    r.s_t1 = reinterpret_cast<const T*>(a.s_t1)[i];
+    r.y = a.target[i];
+    if (NET == ORP_NET_RP) {
+        r.f1 = a.feat1 ? a.feat1[i] : 1.f;
+        r.f2 = a.feat2 ? a.feat2[i] : 0.f;
+    }
+}
+
+template <int NET, typename T>
+__device__ __forceinline__ void unpack_raw(const FitArgs& a, const RawSample<NET, T>& r, float (&x)[Net<NET>::IN], float& s_t1) {
+    x[0] = (float)((double)r.s_t * a.inv_scale);          // divide in fp64, then Keras' cast
+    s_t1 = (float)((double)r.s_t1 * a.inv_scale);
+    if (NET == ORP_NET_RP) { x[1] = r.f1; x[Net<NET>::IN - 1] = r.f2; }
+}
+
+// A block walks tiles of kFitThreads * U consecutive samples (thread t owns samples t, t + 256, ... of the
+// tile: every load is a full-line warp access).  The loads of the NEXT tile are issued before the arithmetic
+// of the current one, so their HBM latency hides behind U x ~250 issue slots per warp: at 8 warps per SM
+// (the 97/122 gradient accumulators take the register file) there is no other warp to switch to.
+template <int NET> constexpr int kFitUnroll = NET == ORP_NET_EO ? 4 : 2;
+
 template <int NET, int LOSS, typename T>
 __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, const float* __restrict__ params,
                                                                const double* __restrict__ state, double* __restrict__ partials) {
     using N = Net<NET>;
+    constexpr int U = kFitUnroll<NET>;
     if (state[ST_STOP] != 0.0) return;
-    __shared__ __align__(16) float s_w[ORP_FIT_MAX_PARAMS];
-    if (threadIdx.x < N::P) s_w[threadIdx.x] = params[threadIdx.x];
+    __shared__ __align__(16) float s_w[kSmemW];
+    load_weights<NET>(s_w, params, threadIdx.x, kFitThreads);
     __syncthreads();
+    const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
 
-    float g[N::P];
-#pragma unroll
-    for (int k = 0; k < N::P; ++k) g[k] = 0.f;
+    Grads<NET> g;
+    g.zero();
     float loss = 0.f;
-    uint64_t n = 0;
-    for (uint64_t i = (uint64_t)blockIdx.x * kFitThreads + threadIdx.x; i < a.count; i += (uint64_t)gridDim.x * kFitThreads) {
-        float x[N::IN], s_t, s_t1, pre1[kH], h1[kH], pre2[kH], h2[kH], phi, psi, l, dv;
-        load_sample<NET, T>(a, i, x, s_t, s_t1);
-        const float v = net_forward<NET>(s_w, x, s_t1, a.b_t1, pre1, h1, pre2, h2, phi, psi);
-        loss_grad<LOSS>(a.target[i], v, l, dv);
-        loss += l;
-        net_backward<NET>(s_w, x, s_t1, a.b_t1, dv, pre1, h1, pre2, h2, g);
-        ++n;
+    uint32_t n = 0;
+    const uint64_t tile = (uint64_t)kFitThreads * U, stride = (uint64_t)gridDim.x * tile;
+    uint64_t base = (uint64_t)blockIdx.x * tile + threadIdx.x;
+    RawSample<NET, T> cur[U], nxt[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        cur[u] = RawSample<NET, T>{};
+        if (base + (uint64_t)u * kFitThreads < a.count) load_raw<NET, T>(a, base + (uint64_t)u * kFitThreads, cur[u]);
     }
-    block_reduce_to<N::P>(g, loss, n, partials + (size_t)blockIdx.x * kGsum);
+    for (; base < a.count + threadIdx.x; base += stride) {        // block-uniform trip count (base - threadIdx.x < count)
+        const uint64_t nb = base + stride;
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            nxt[u] = RawSample<NET, T>{};
+            if (nb + (uint64_t)u * kFitThreads < a.count) load_raw<NET, T>(a, nb + (uint64_t)u * kFitThreads, nxt[u]);
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (base + (uint64_t)u * kFitThreads < a.count) {
+                float x[N::IN], s_t1, phi, psi, l, dv;
+                Acts<NET> act;
+                unpack_raw<NET, T>(a, cur[u], x, s_t1);
+                const float v = net_forward<NET>(s_wa, x, s_t1, a.b_t1, act, phi, psi);
+                loss_grad<LOSS>(cur[u].y, v, l, dv);
+                loss += l;
+                net_backward<NET>(s_wa, x, s_t1, a.b_t1, dv, act, g);
+                ++n;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) cur[u] = nxt[u];
+    }
+    block_reduce_to<NET>(g, loss, n, partials + (size_t)blockIdx.x * kGsum);
 }
 
 // Fixed-order sum of the per-block partials: lane l adds blocks l, l+32, ... in increasing order, then a
@@ -292,17 +477,19 @@ __global__ void fit_end_kernel(int P, float* __restrict__ params, double* __rest
 
 // a-10 / a-11: roll-back values at prices@t and the hedge-weight sums.
 template <int NET, typename T>
-__global__ void __launch_bounds__(kFitThreads) fit_predict_kernel(const FitArgs a, const float* __restrict__ params,
+__global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitArgs a, const float* __restrict__ params,
                                                                   float* __restrict__ values_out, double* __restrict__ partials) {
     using N = Net<NET>;
-    __shared__ __align__(16) float s_w[ORP_FIT_MAX_PARAMS];
-    if (threadIdx.x < N::P) s_w[threadIdx.x] = params[threadIdx.x];
+    __shared__ __align__(16) float s_w[kSmemW];
+    load_weights<NET>(s_w, params, threadIdx.x, kFitThreads);
     __syncthreads();
+    const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
     double sv = 0.0, sphi = 0.0, spsi = 0.0, sae = 0.0;
     for (uint64_t i = (uint64_t)blockIdx.x * kFitThreads + threadIdx.x; i < a.count; i += (uint64_t)gridDim.x * kFitThreads) {
-        float x[N::IN], s_t, s_t1, pre1[kH], h1[kH], pre2[kH], h2[kH], phi, psi;
+        float x[N::IN], s_t, s_t1, phi, psi;
+        Acts<NET> act;
         load_sample<NET, T>(a, i, x, s_t, s_t1);
-        net_forward<NET>(s_w, x, s_t, a.b_t, pre1, h1, pre2, h2, phi, psi);
+        net_forward<NET>(s_wa, x, s_t, a.b_t, act, phi, psi);
         const float v0 = fmaf(phi, s_t, psi * a.b_t);            // model.predict(X0): prices at t
         const float v1 = fmaf(phi, s_t1, psi * a.b_t1);          // model.predict(X1): prices at t+1
         if (values_out) values_out[i] = v0;
@@ -354,12 +541,13 @@ __global__ void __launch_bounds__(kMiniThreads, 1) fit_minibatch_kernel(const Fi
                                                                         uint64_t epoch_seed) {
     using N = Net<NET>;
     if (state[ST_STOP] != 0.0) return;
-    __shared__ __align__(16) float s_w[ORP_FIT_MAX_PARAMS];
+    __shared__ __align__(16) float s_w[kSmemW];
     __shared__ float s_red[kMiniThreads / 32][N::P + 1];
     __shared__ float s_lr, s_t;
     __shared__ double s_loss;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid < N::P) s_w[tid] = params[tid];
+    load_weights<NET>(s_w, params, tid, kMiniThreads);
+    const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
     float m = 0.f, v = 0.f;
     if (tid < N::P) { m = (float)state[ST_ADAM_M + tid]; v = (float)state[ST_ADAM_V + tid]; }
     if (tid == 0) {
@@ -376,24 +564,24 @@ __global__ void __launch_bounds__(kMiniThreads, 1) fit_minibatch_kernel(const Fi
 
     for (uint64_t b0 = 0; b0 < a.count; b0 += batch_size) {
         const int nb = (int)min((uint64_t)batch_size, a.count - b0);
-        float g[N::P];
-#pragma unroll
-        for (int k = 0; k < N::P; ++k) g[k] = 0.f;
+        Grads<NET> g;
+        g.zero();
         float loss = 0.f;
         for (int r = tid; r < nb; r += kMiniThreads) {
             // position b0 + r of the epoch's permutation (cycle-walk down from the enclosing power of two)
             uint64_t i = perm_pow2(b0 + r, bits, epoch_seed);
             while (i >= a.count) i = perm_pow2(i, bits, epoch_seed);
-            float x[N::IN], s_t_, s_t1, pre1[kH], h1[kH], pre2[kH], h2[kH], phi, psi, l, dv;
+            float x[N::IN], s_t_, s_t1, phi, psi, l, dv;
+            Acts<NET> act;
             load_sample<NET, T>(a, i, x, s_t_, s_t1);
-            const float vv = net_forward<NET>(s_w, x, s_t1, a.b_t1, pre1, h1, pre2, h2, phi, psi);
+            const float vv = net_forward<NET>(s_wa, x, s_t1, a.b_t1, act, phi, psi);
             loss_grad<LOSS>(a.target[i], vv, l, dv);
             loss += l;
-            net_backward<NET>(s_w, x, s_t1, a.b_t1, dv, pre1, h1, pre2, h2, g);
+            net_backward<NET>(s_wa, x, s_t1, a.b_t1, dv, act, g);
         }
 #pragma unroll
         for (int k = 0; k < N::P; ++k) {
-            float t = g[k];
+            float t = g.get(k);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
             if (lane == 0) s_red[warp][k] = t;
@@ -412,7 +600,12 @@ __global__ void __launch_bounds__(kMiniThreads, 1) fit_minibatch_kernel(const Fi
                 const float lr_t = (float)(lr * sqrt(1.0 - pow(0.999, adam_t)) / (1.0 - pow(0.9, adam_t)));
                 m = 0.9f * m + (1.f - 0.9f) * grad;
                 v = 0.999f * v + (1.f - 0.999f) * grad * grad;
-                s_w[tid] -= lr_t * m / (sqrtf(v) + 1e-7f);
+                const float wn = s_w[tid] - lr_t * m / (sqrtf(v) + 1e-7f);
+                s_w[tid] = wn;
+                if (tid >= N::W2 && tid < N::W2 + kH * kH) {       // keep the transposed copy in step
+                    const int k = tid - N::W2;
+                    s_w[kW2T + (k & 7) * kH + (k >> 3)] = wn;
+                }
             } else {
                 s_loss += (double)t;                  // Keras: epoch loss = sample-weighted mean of batch losses
             }
@@ -428,8 +621,9 @@ __global__ void __launch_bounds__(kMiniThreads, 1) fit_minibatch_kernel(const Fi
     }
 }
 
-static int fit_blocks(uint64_t count) {
-    uint64_t want = (count + kFitThreads - 1) / kFitThreads;
+static int fit_blocks(uint64_t count, int unroll) {
+    const uint64_t tile = (uint64_t)kFitThreads * unroll;
+    uint64_t want = (count + tile - 1) / tile;
     if (want < 1) want = 1;
     uint64_t cap = (uint64_t)sm_count();           // 256 threads x ~200 registers: one block per SM
     if (cap > 512) cap = 512;
@@ -479,7 +673,7 @@ extern "C" int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const
     if (rc) return rc;
     ORP_REQUIRE(d_params && d_state && d_gsum && d_scratch, "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
-    const int grid = fit_blocks(a.count);
+    const int grid = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
     double* partials = reinterpret_cast<double*>(d_scratch);
 #define CALL_GRAD(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T><<<grid, kFitThreads, 0, st>>>(a, d_params, d_state, partials)
     ORP_FIT_DISPATCH(CALL_GRAD);
