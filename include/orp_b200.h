@@ -125,6 +125,24 @@ int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, uint64_t coun
                       const double* strikes, const int32_t* cols, double s0, double value_scale,
                       float* d_values_out, double* d_sums, double* d_otm, void* d_scratch, void* stream);
 
+/* No counterpart in the reference.  Same computation and results as orp_payoff_reduce for callers that cannot
+ * allocate device memory when they price — e.g. a service that gives all of the GPU to fixed arenas at start-up
+ * and bans the runtime allocator afterwards, or a plug-in inside a framework whose allocator it may not use — and
+ * therefore cannot supply d_scratch.  The per-block partial sums go to a fixed 128 KiB array inside the library
+ * image instead (resident on every GPU that loads the library, until the process exits).  The caller still
+ * passes inputs and outputs.  Limits and rules:
+ *   - at most ORP_PAYOFF_NOALLOC_MAX_OPTIONS options per call; more is refused with ORP_E_VALUE (split the
+ *     options over several calls, or use orp_payoff_reduce);
+ *   - the first call on each device looks up the array's device address (no allocation); make that first call
+ *     before starting any stream capture on that device;
+ *   - all calls share the one array: two calls whose kernels may run at the same time on a GPU (different
+ *     streams, different host threads) race on it — serialise them.  Nothing has to be cleared between calls;
+ *   - the entry point itself never calls cudaMalloc / cudaFree or any allocating routine. */
+#define ORP_PAYOFF_NOALLOC_MAX_OPTIONS 8
+int orp_payoff_reduce_noalloc(const void* d_paths, int dtype, uint64_t ld, uint64_t count, int kind, int n_opt,
+                              const double* strikes, const int32_t* cols, double s0, double value_scale,
+                              float* d_values_out, double* d_sums, double* d_otm, void* stream);
+
 /* ---------------------------------------------------------------- a-9/10/11  replicating-portfolio fit (device) */
 
 enum { ORP_NET_EO = 0, ORP_NET_RP = 1 };       /* 1->8->8->1 (psi = 1 - phi), 97 params; 3->8->8->2, 122 params */

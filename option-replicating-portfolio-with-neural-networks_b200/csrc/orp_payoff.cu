@@ -6,6 +6,8 @@
 // result does not depend on scheduling (and matches on every launch bit for bit).
 #include "orp_common.h"
 
+#include <mutex>
+
 namespace orp {
 
 constexpr int kPayThreads = 256;
@@ -132,5 +134,80 @@ extern "C" int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, ui
     ORP_LAUNCH_CHECK("payoff_partial_kernel");
     payoff_final_kernel<<<(2 * n_opt + 127) / 128, 128, 0, st>>>(a.partials, gx, n_opt, d_sums, d_otm);
     ORP_LAUNCH_CHECK("payoff_final_kernel");
+    return ORP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of orp_payoff_reduce (no counterpart in the reference).
+//
+// Who needs it: a caller that cannot obtain device memory at the time it wants a price — a pricing service
+// that hands its whole GPU budget to fixed arenas at start-up and forbids the runtime allocator afterwards,
+// or a plug-in living inside another framework whose allocator it may not touch.  Such a caller still owns
+// its inputs (the path array) and outputs (the sums), but has nowhere to put the per-block partial sums the
+// regular entry point expects in `d_scratch`.  Here those partials live in a fixed array that is part of
+// the library image: every GPU that loads liborp_b200.so carries these 128 KiB until the process exits.
+//
+// The array's name below is only a host-side handle; its device address is looked up once per device with
+// cudaGetSymbolAddress (with that device current) and that address is what the kernels receive.
+constexpr int kNoAllocBlocks = 1024;          // upper bound of the grid's x extent (payoff_blocks() <= 1024)
+static_assert(ORP_PAYOFF_NOALLOC_MAX_OPTIONS == kPayChunk, "one chunk of options: 1024 blocks x 16 doubles");
+static __device__ __align__(256) double g_payoff_noalloc_partials[kNoAllocBlocks * 2 * kPayChunk];
+
+// Device address of the array on the CURRENT device (cached per device ordinal).
+static int noalloc_partials(double** out) {
+    static std::mutex mu;
+    static double* cached[64] = {nullptr};
+    int dev = 0;
+    ORP_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return orp::fail(ORP_E_STATE, "device ordinal %d is outside the supported range [0, 64)", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!cached[dev]) {
+        void* p = nullptr;
+        ORP_CUDA(cudaGetSymbolAddress(&p, g_payoff_noalloc_partials));
+        if (!p) return orp::fail(ORP_E_STATE, "cudaGetSymbolAddress returned a null address for the static scratch");
+        cached[dev] = static_cast<double*>(p);
+    }
+    *out = cached[dev];
+    return ORP_OK;
+}
+
+extern "C" int orp_payoff_reduce_noalloc(const void* d_paths, int dtype, uint64_t ld, uint64_t count, int kind, int n_opt,
+                                         const double* strikes, const int32_t* cols, double s0, double value_scale,
+                                         float* d_values_out, double* d_sums, double* d_otm, void* stream) {
+    ORP_REQUIRE(d_paths && strikes && cols && d_sums && d_otm, "null pointer");
+    ORP_REQUIRE(n_opt >= 1, "n_opt must be >= 1");
+    ORP_REQUIRE(n_opt <= ORP_PAYOFF_NOALLOC_MAX_OPTIONS,
+                "orp_payoff_reduce_noalloc handles at most %d options per call (got %d): its scratch is a fixed %zu-byte "
+                "array inside the library; split the options over several calls or use orp_payoff_reduce",
+                ORP_PAYOFF_NOALLOC_MAX_OPTIONS, n_opt, sizeof(double) * kNoAllocBlocks * 2 * kPayChunk);
+    ORP_REQUIRE(kind >= ORP_PAYOFF_CALL && kind <= ORP_PAYOFF_FLOOR, "unknown payoff kind %d", kind);
+    ORP_REQUIRE(dtype == ORP_F64 || dtype == ORP_F32, "dtype must be ORP_F64 or ORP_F32");
+    ORP_REQUIRE(ld >= count, "ld must be >= count");
+    double* partials = nullptr;
+    int rc = noalloc_partials(&partials);        // first call on a device: symbol look-up (no allocation)
+    if (rc) return rc;
+    PayoffArgs a;
+    a.paths = d_paths; a.ld = ld; a.count = count; a.kind = kind; a.n_opt = n_opt;
+    a.s0 = s0; a.value_scale = value_scale; a.values_out = d_values_out;
+    a.partials = partials;
+    for (int k = 0; k < n_opt; ++k) {
+        ORP_REQUIRE(cols[k] >= 0, "negative column index");
+        a.strikes[k] = strikes[k];
+        a.cols[k] = cols[k];
+    }
+    uint64_t want = (count + kPayThreads - 1) / kPayThreads;
+    if (want < 1) want = 1;
+    int gx = payoff_blocks();
+    if (gx > kNoAllocBlocks) gx = kNoAllocBlocks;
+    if ((uint64_t)gx > want) gx = (int)want;
+    cudaStream_t st = (cudaStream_t)stream;
+    // Nothing in the array has to start at zero: every block of this launch overwrites its own 16 slots and the
+    // second kernel reads exactly those gx blocks, so what an earlier call left behind is never looked at.
+    dim3 grid(gx, 1);
+    if (dtype == ORP_F64) payoff_partial_kernel<double><<<grid, kPayThreads, 0, st>>>(a);
+    else                  payoff_partial_kernel<float><<<grid, kPayThreads, 0, st>>>(a);
+    ORP_LAUNCH_CHECK("payoff_partial_kernel (noalloc)");
+    payoff_final_kernel<<<(2 * n_opt + 127) / 128, 128, 0, st>>>(partials, gx, n_opt, d_sums, d_otm);
+    ORP_LAUNCH_CHECK("payoff_final_kernel (noalloc)");
     return ORP_OK;
 }
