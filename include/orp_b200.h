@@ -188,6 +188,18 @@ int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const double* d_
 #define ORP_FIT_EPOCH_LAST 2
 int orp_fit_update(int net, float* d_params, double* d_state, const double* d_gsum, int flags, void* stream);
 
+/* Single-GPU form of one optimiser step: orp_fit_grad + the fixed-order reduction + orp_fit_update in ONE launch
+ * (the thread block that finishes last reduces and updates; results are bit-identical to the two-stage form).
+ * Same place in Model.fit's inner loop (Replicating_Portfolio.py:211).  d_gsum receives the reduced vector. */
+int orp_fit_step(const orp_fit_batch* b, float* d_params, double* d_state, double* d_gsum, void* d_scratch,
+                 int flags, void* stream);
+
+/* Enqueues n_epochs epochs of n_parts single-launch steps each (parts[k] = the k-th batch of every epoch, flags
+ * set as above) without returning to the caller in between: the epoch loop of Model.fit (Replicating_Portfolio.py:211).
+ * Epochs after the stop flag is raised are no-ops on the device. */
+int orp_fit_epochs(const orp_fit_batch* parts, int n_parts, float* d_params, double* d_state, double* d_gsum,
+                   void* d_scratch, int n_epochs, void* stream);
+
 /* Starts a Model.fit call: resets the early-stopping state, keeps weights and Adam moments (they persist across
  * time steps, Replicating_Portfolio.py:203-211).  use_schedule = 1 for the first fit. */
 int orp_fit_begin(double* d_state, int epochs, int patience, int use_schedule, void* stream);

@@ -16,7 +16,8 @@ enum {
     ST_LR = 0, ST_ADAM_T, ST_EPOCH, ST_EPOCHS, ST_PATIENCE, ST_USE_SCHED, ST_WAIT, ST_BEST, ST_STOP,
     ST_STOPPED_EARLY, ST_LAST_LOSS, ST_EPOCHS_RUN, ST_HAVE_BEST, ST_TOTAL_EPOCHS, ST_LOSS_ACC, ST_COUNT_ACC,
     ST_ADAM_M = 16, ST_ADAM_V = ST_ADAM_M + ORP_FIT_MAX_PARAMS, ST_BEST_W = ST_ADAM_V + ORP_FIT_MAX_PARAMS,
-    ST_END = ST_BEST_W + ORP_FIT_MAX_PARAMS
+    ST_TICKET = ST_BEST_W + ORP_FIT_MAX_PARAMS,      // block-arrival counter of the single-launch step (used as uint32)
+    ST_END = ST_TICKET + 1
 };
 static_assert(ST_END <= ORP_FIT_STATE_DOUBLES, "state block too small");
 
@@ -101,63 +102,96 @@ __device__ __forceinline__ void load_weights(float* __restrict__ s_w, const floa
     for (int k = tid; k < kH * kH; k += nthreads) s_w[kW2T + (k & 7) * kH + (k >> 3)] = params[N::W2 + k];   // k = i*8+j -> [j][i]
 }
 
-template <int NET> struct Acts {
-    f2 pre1[kH / 2], h1[kH / 2], pre2[kH / 2], h2[kH / 2];
+// S samples are carried through the network TOGETHER by one thread: every weight pair is read from shared
+// memory once and used S times (halving the LDS traffic, which otherwise runs at 60 % of the LSU pipe), and the
+// S independent dependency chains fill the FFMA2 latency that 8 warps per SM cannot hide by switching.
+// Only the post-activation values are kept: LeakyReLU preserves the sign, so the slope is read off h.
+template <int NET, int S> struct Acts {
+    f2 h1[S][kH / 2], h2[S][kH / 2];
 };
 
-// Forward pass; returns V, phi/psi and the activations needed by the backward pass.  `w` is the shared-space
-// address of the weight image.
-template <int NET>
-__device__ __forceinline__ float net_forward(uint32_t w, const float (&x)[Net<NET>::IN], float p0, float p1,
-                                             Acts<NET>& a, float& phi, float& psi) {
+// Forward pass: V[s] = phi[s] p0[s] + psi[s] p1.  `w` is the shared-space address of the weight image.
+template <int NET, int S>
+__device__ __forceinline__ void net_forward(uint32_t w, const float (&x)[S][Net<NET>::IN], const float (&p0)[S], float p1,
+                                            Acts<NET, S>& a, float (&phi)[S], float (&psi)[S], float (&v)[S]) {
     using N = Net<NET>;
     static_assert(N::W1 % 4 == 0 && N::B1 % 4 == 0 && N::W2 % 4 == 0 && N::B2 % 4 == 0 && N::W3 % 4 == 0 && N::B3 % 2 == 0,
                   "parameter blocks must be 16-byte aligned for the paired loads");
+    f2 pre[S][kH / 2];
 #pragma unroll
-    for (int q = 0; q < kH / 4; ++q) { const f2x2 b = ldw(w, N::B1 / 2 + 2 * q); a.pre1[2 * q] = b.a; a.pre1[2 * q + 1] = b.b; }
+    for (int q = 0; q < kH / 4; ++q) {
+        const f2x2 b = ldw(w, N::B1 / 2 + 2 * q);
+#pragma unroll
+        for (int s = 0; s < S; ++s) { pre[s][2 * q] = b.a; pre[s][2 * q + 1] = b.b; }
+    }
 #pragma unroll
     for (int i = 0; i < N::IN; ++i)
 #pragma unroll
         for (int q = 0; q < kH / 4; ++q) {
             const f2x2 c = ldw(w, (N::W1 + i * kH) / 2 + 2 * q);
-            a.pre1[2 * q] = fma2s(x[i], c.a, a.pre1[2 * q]);
-            a.pre1[2 * q + 1] = fma2s(x[i], c.b, a.pre1[2 * q + 1]);
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                pre[s][2 * q] = fma2s(x[s][i], c.a, pre[s][2 * q]);
+                pre[s][2 * q + 1] = fma2s(x[s][i], c.b, pre[s][2 * q + 1]);
+            }
         }
 #pragma unroll
-    for (int q = 0; q < kH / 4; ++q) { const f2x2 b = ldw(w, N::B2 / 2 + 2 * q); a.pre2[2 * q] = b.a; a.pre2[2 * q + 1] = b.b; }
+    for (int s = 0; s < S; ++s)
 #pragma unroll
-    for (int jp = 0; jp < kH / 2; ++jp) a.h1[jp] = lrelu2(a.pre1[jp]);
+        for (int jp = 0; jp < kH / 2; ++jp) a.h1[s][jp] = lrelu2(pre[s][jp]);
 #pragma unroll
-    for (int i = 0; i < kH; ++i) {
-        const float hi = elem(a.h1, i);
+    for (int q = 0; q < kH / 4; ++q) {
+        const f2x2 b = ldw(w, N::B2 / 2 + 2 * q);
+#pragma unroll
+        for (int s = 0; s < S; ++s) { pre[s][2 * q] = b.a; pre[s][2 * q + 1] = b.b; }
+    }
+#pragma unroll
+    for (int i = 0; i < kH; ++i)
 #pragma unroll
         for (int q = 0; q < kH / 4; ++q) {
             const f2x2 c = ldw(w, (N::W2 + i * kH) / 2 + 2 * q);
-            a.pre2[2 * q] = fma2s(hi, c.a, a.pre2[2 * q]);
-            a.pre2[2 * q + 1] = fma2s(hi, c.b, a.pre2[2 * q + 1]);
-        }
-    }
 #pragma unroll
-    for (int jp = 0; jp < kH / 2; ++jp) a.h2[jp] = lrelu2(a.pre2[jp]);
+            for (int s = 0; s < S; ++s) {
+                const float hi = elem(a.h1[s], i);
+                pre[s][2 * q] = fma2s(hi, c.a, pre[s][2 * q]);
+                pre[s][2 * q + 1] = fma2s(hi, c.b, pre[s][2 * q + 1]);
+            }
+        }
+#pragma unroll
+    for (int s = 0; s < S; ++s)
+#pragma unroll
+        for (int jp = 0; jp < kH / 2; ++jp) a.h2[s][jp] = lrelu2(pre[s][jp]);
     if (NET == ORP_NET_EO) {
         const f2x2 c0 = ldw(w, N::W3 / 2), c1 = ldw(w, N::W3 / 2 + 2);        // phi = b3 + sum_i h2[i] w3[i], pairs over i
-        f2 s = mul2(a.h2[0], c0.a);
-        s = fma2(a.h2[1], c0.b, s);
-        s = fma2(a.h2[2], c1.a, s);
-        s = fma2(a.h2[3], c1.b, s);
-        phi = ldw1(w, N::B3) + (s.x + s.y);
-        psi = 1.f - phi;
+        const float b3 = ldw1(w, N::B3);
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            f2 t = mul2(a.h2[s][0], c0.a);
+            t = fma2(a.h2[s][1], c0.b, t);
+            t = fma2(a.h2[s][2], c1.a, t);
+            t = fma2(a.h2[s][3], c1.b, t);
+            phi[s] = b3 + (t.x + t.y);
+            psi[s] = 1.f - phi[s];
+        }
     } else {
-        f2 o = make_float2(ldw1(w, N::B3), ldw1(w, N::B3 + 1));               // (phi, psi) = b3 + sum_i h2[i] W3[i][0:2]
+        f2 o[S];
+        const f2 b3 = make_float2(ldw1(w, N::B3), ldw1(w, N::B3 + 1));        // (phi, psi) = b3 + sum_i h2[i] W3[i][0:2]
+#pragma unroll
+        for (int s = 0; s < S; ++s) o[s] = b3;
 #pragma unroll
         for (int q = 0; q < kH / 2; ++q) {
             const f2x2 c = ldw(w, N::W3 / 2 + 2 * q);
-            o = fma2s(elem(a.h2, 2 * q), c.a, o);
-            o = fma2s(elem(a.h2, 2 * q + 1), c.b, o);
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                o[s] = fma2s(elem(a.h2[s], 2 * q), c.a, o[s]);
+                o[s] = fma2s(elem(a.h2[s], 2 * q + 1), c.b, o[s]);
+            }
         }
-        phi = o.x; psi = o.y;
+#pragma unroll
+        for (int s = 0; s < S; ++s) { phi[s] = o[s].x; psi[s] = o[s].y; }
     }
-    return fmaf(phi, p0, psi * p1);
+#pragma unroll
+    for (int s = 0; s < S; ++s) v[s] = fmaf(phi[s], p0[s], psi[s] * p1);
 }
 
 // Gradient accumulators of one thread, as pairs in the order of the parameter vector.
@@ -175,69 +209,95 @@ template <int NET> struct Grads {
     }
 };
 
-// Backward pass of V = phi p0 + psi p1 for one sample, accumulating into g.
-template <int NET>
-__device__ __forceinline__ void net_backward(uint32_t w, const float (&x)[Net<NET>::IN], float p0, float p1,
-                                             float dV, const Acts<NET>& a, Grads<NET>& g) {
+// Backward pass of V = phi p0 + psi p1 for S samples, accumulating into g.  dV[s] = 0 switches a sample off.
+template <int NET, int S>
+__device__ __forceinline__ void net_backward(uint32_t w, const float (&x)[S][Net<NET>::IN], const float (&p0)[S], float p1,
+                                             const float (&dV)[S], const Acts<NET, S>& a, Grads<NET>& g) {
     using N = Net<NET>;
-    f2 d2[kH / 2];
+    f2 d2[S][kH / 2];
     if (NET == ORP_NET_EO) {
-        const float dphi = dV * (p0 - p1);                                    // psi = 1 - phi
-        const f2 dd = make_float2(dphi, dphi);
+        f2 dd[S];
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const float dphi = dV[s] * (p0[s] - p1);                          // psi = 1 - phi
+            dd[s] = make_float2(dphi, dphi);
+            g.last += dphi;
+        }
 #pragma unroll
         for (int q = 0; q < kH / 4; ++q) {
             const f2x2 c = ldw(w, N::W3 / 2 + 2 * q);
-            g.v[N::W3 / 2 + 2 * q] = fma2(dd, a.h2[2 * q], g.v[N::W3 / 2 + 2 * q]);
-            g.v[N::W3 / 2 + 2 * q + 1] = fma2(dd, a.h2[2 * q + 1], g.v[N::W3 / 2 + 2 * q + 1]);
-            d2[2 * q] = mul2(mul2(dd, c.a), dlrelu2(a.pre2[2 * q]));
-            d2[2 * q + 1] = mul2(mul2(dd, c.b), dlrelu2(a.pre2[2 * q + 1]));
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                g.v[N::W3 / 2 + 2 * q] = fma2(dd[s], a.h2[s][2 * q], g.v[N::W3 / 2 + 2 * q]);
+                g.v[N::W3 / 2 + 2 * q + 1] = fma2(dd[s], a.h2[s][2 * q + 1], g.v[N::W3 / 2 + 2 * q + 1]);
+                d2[s][2 * q] = mul2(mul2(dd[s], c.a), dlrelu2(a.h2[s][2 * q]));
+                d2[s][2 * q + 1] = mul2(mul2(dd[s], c.b), dlrelu2(a.h2[s][2 * q + 1]));
+            }
         }
-        g.last += dphi;
     } else {
-        const f2 dout = make_float2(dV * p0, dV * p1);
-        float d2s[kH];
+        f2 dout[S];
+        float d2s[S][kH];
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            dout[s] = make_float2(dV[s] * p0[s], dV[s] * p1);
+            g.v[N::B3 / 2] = add2(g.v[N::B3 / 2], dout[s]);
+        }
 #pragma unroll
         for (int q = 0; q < kH / 2; ++q) {
             const f2x2 c = ldw(w, N::W3 / 2 + 2 * q);
-            g.v[N::W3 / 2 + 2 * q] = fma2s(elem(a.h2, 2 * q), dout, g.v[N::W3 / 2 + 2 * q]);
-            g.v[N::W3 / 2 + 2 * q + 1] = fma2s(elem(a.h2, 2 * q + 1), dout, g.v[N::W3 / 2 + 2 * q + 1]);
-            const f2 t0 = mul2(dout, c.a), t1 = mul2(dout, c.b);
-            d2s[2 * q] = t0.x + t0.y;
-            d2s[2 * q + 1] = t1.x + t1.y;
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                g.v[N::W3 / 2 + 2 * q] = fma2s(elem(a.h2[s], 2 * q), dout[s], g.v[N::W3 / 2 + 2 * q]);
+                g.v[N::W3 / 2 + 2 * q + 1] = fma2s(elem(a.h2[s], 2 * q + 1), dout[s], g.v[N::W3 / 2 + 2 * q + 1]);
+                const f2 t0 = mul2(dout[s], c.a), t1 = mul2(dout[s], c.b);
+                d2s[s][2 * q] = t0.x + t0.y;
+                d2s[s][2 * q + 1] = t1.x + t1.y;
+            }
         }
 #pragma unroll
-        for (int ip = 0; ip < kH / 2; ++ip) d2[ip] = mul2(make_float2(d2s[2 * ip], d2s[2 * ip + 1]), dlrelu2(a.pre2[ip]));
-        g.v[N::B3 / 2] = add2(g.v[N::B3 / 2], dout);
+        for (int s = 0; s < S; ++s)
+#pragma unroll
+            for (int ip = 0; ip < kH / 2; ++ip)
+                d2[s][ip] = mul2(make_float2(d2s[s][2 * ip], d2s[s][2 * ip + 1]), dlrelu2(a.h2[s][ip]));
     }
-    f2 d1[kH / 2];
+    f2 d1[S][kH / 2];
 #pragma unroll
-    for (int ip = 0; ip < kH / 2; ++ip) d1[ip] = make_float2(0.f, 0.f);
+    for (int s = 0; s < S; ++s)
 #pragma unroll
-    for (int j = 0; j < kH; ++j) {                                            // d1[i] = sum_j d2[j] W2[i][j], pairs over i
-        const float dj = elem(d2, j);
+        for (int ip = 0; ip < kH / 2; ++ip) d1[s][ip] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int j = 0; j < kH; ++j)                                              // d1[i] = sum_j d2[j] W2[i][j], pairs over i
 #pragma unroll
         for (int q = 0; q < kH / 4; ++q) {
             const f2x2 c = ldw(w, (kW2T + j * kH) / 2 + 2 * q);
-            d1[2 * q] = fma2s(dj, c.a, d1[2 * q]);
-            d1[2 * q + 1] = fma2s(dj, c.b, d1[2 * q + 1]);
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                const float dj = elem(d2[s], j);
+                d1[s][2 * q] = fma2s(dj, c.a, d1[s][2 * q]);
+                d1[s][2 * q + 1] = fma2s(dj, c.b, d1[s][2 * q + 1]);
+            }
         }
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+#pragma unroll
+        for (int i = 0; i < kH; ++i) {                                        // dW2[i][j] += h1[i] d2[j], pairs over j
+            const float hi = elem(a.h1[s], i);
+#pragma unroll
+            for (int jp = 0; jp < kH / 2; ++jp)
+                g.v[(N::W2 + i * kH) / 2 + jp] = fma2s(hi, d2[s][jp], g.v[(N::W2 + i * kH) / 2 + jp]);
+        }
+#pragma unroll
+        for (int jp = 0; jp < kH / 2; ++jp) {
+            d1[s][jp] = mul2(d1[s][jp], dlrelu2(a.h1[s][jp]));
+            g.v[N::B2 / 2 + jp] = add2(g.v[N::B2 / 2 + jp], d2[s][jp]);
+            g.v[N::B1 / 2 + jp] = add2(g.v[N::B1 / 2 + jp], d1[s][jp]);
+        }
+#pragma unroll
+        for (int i = 0; i < N::IN; ++i)
+#pragma unroll
+            for (int jp = 0; jp < kH / 2; ++jp)
+                g.v[(N::W1 + i * kH) / 2 + jp] = fma2s(x[s][i], d1[s][jp], g.v[(N::W1 + i * kH) / 2 + jp]);
     }
-#pragma unroll
-    for (int i = 0; i < kH; ++i) {                                            // dW2[i][j] += h1[i] d2[j], pairs over j
-        const float hi = elem(a.h1, i);
-#pragma unroll
-        for (int jp = 0; jp < kH / 2; ++jp) g.v[(N::W2 + i * kH) / 2 + jp] = fma2s(hi, d2[jp], g.v[(N::W2 + i * kH) / 2 + jp]);
-    }
-#pragma unroll
-    for (int jp = 0; jp < kH / 2; ++jp) {
-        d1[jp] = mul2(d1[jp], dlrelu2(a.pre1[jp]));
-        g.v[N::B2 / 2 + jp] = add2(g.v[N::B2 / 2 + jp], d2[jp]);
-        g.v[N::B1 / 2 + jp] = add2(g.v[N::B1 / 2 + jp], d1[jp]);
-    }
-#pragma unroll
-    for (int i = 0; i < N::IN; ++i)
-#pragma unroll
-        for (int jp = 0; jp < kH / 2; ++jp) g.v[(N::W1 + i * kH) / 2 + jp] = fma2s(x[i], d1[jp], g.v[(N::W1 + i * kH) / 2 + jp]);
 }
 
 // per-sample loss and dLoss/dV (without the 1/N of the batch mean)
@@ -269,8 +329,96 @@ __device__ __forceinline__ void load_sample(const FitArgs& a, uint64_t i, float 
     }
 }
 
+constexpr int kGsumLen = ORP_FIT_MAX_PARAMS + 2;   // grads, loss sum, count
+
+__device__ __forceinline__ double schedule_lr(int epoch, double lr) {      // Replicating_Portfolio.py:128-136
+    if (epoch < 100) return 1e-2;
+    if (epoch < 200) return 1e-3;
+    if (epoch < 400) return 5e-4;
+    return lr;
+}
+
+// Adam (Keras: lr_t = lr sqrt(1-b2^t)/(1-b1^t); w -= lr_t m / (sqrt(v) + 1e-7)), fp32 like the Keras variables.
+__device__ __forceinline__ void adam_apply(float* __restrict__ params, double* __restrict__ state, int k, float grad,
+                                           float lr_t) {
+    float m = (float)state[ST_ADAM_M + k], v = (float)state[ST_ADAM_V + k];
+    m = 0.9f * m + (1.f - 0.9f) * grad;
+    v = 0.999f * v + (1.f - 0.999f) * grad * grad;
+    state[ST_ADAM_M + k] = m;
+    state[ST_ADAM_V + k] = v;
+    params[k] -= lr_t * m / (sqrtf(v) + 1e-7f);
+}
+
+// End-of-epoch callbacks, run by ONE thread after the epoch's updates are visible in params.
+__device__ void epoch_end(int P, const float* __restrict__ params, double* __restrict__ state, double cur) {
+    state[ST_LAST_LOSS] = cur;
+    int epoch = (int)state[ST_EPOCH];
+    double wait = state[ST_WAIT] + 1.0;
+    if (cur < state[ST_BEST]) {                       // EarlyStopping(monitor='loss', min_delta=0)
+        state[ST_BEST] = cur;
+        wait = 0.0;
+        for (int k = 0; k < P; ++k) state[ST_BEST_W + k] = params[k];     // restore_best_weights=True
+        state[ST_HAVE_BEST] = 1.0;
+    }
+    state[ST_WAIT] = wait;
+    if (wait >= state[ST_PATIENCE] && epoch > 0) { state[ST_STOP] = 1.0; state[ST_STOPPED_EARLY] = 1.0; }
+    epoch += 1;
+    state[ST_EPOCH] = epoch;
+    state[ST_EPOCHS_RUN] = epoch;
+    state[ST_TOTAL_EPOCHS] += 1.0;
+    if (epoch >= (int)state[ST_EPOCHS]) state[ST_STOP] = 1.0;
+}
+
+// One optimiser step, run by one block of >= 128 threads (all of them must call).  flags bit 0: first batch of
+// the epoch (LearningRateScheduler.on_epoch_begin), bit 1: last batch (epoch loss = sample-weighted mean of the
+// batch losses, then the callbacks).  gsum may live in shared or global memory.
+__device__ __forceinline__ void optimiser_step(int P, float* __restrict__ params, double* __restrict__ state,
+                                               const double* __restrict__ gsum, int flags) {
+    __shared__ float s_lr_t;
+    if (threadIdx.x == 0) {
+        double lr = state[ST_LR];
+        if ((flags & 1) && state[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)state[ST_EPOCH], lr);
+        state[ST_LR] = lr;
+        const double t = state[ST_ADAM_T] + 1.0;
+        state[ST_ADAM_T] = t;
+        s_lr_t = (float)(lr * sqrt(1.0 - pow(0.999, t)) / (1.0 - pow(0.9, t)));
+    }
+    __syncthreads();
+    const double inv_n = 1.0 / gsum[ORP_FIT_MAX_PARAMS + 1];
+    if (threadIdx.x < P) adam_apply(params, state, threadIdx.x, (float)(gsum[threadIdx.x] * inv_n), s_lr_t);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const double loss_acc = ((flags & 1) ? 0.0 : state[ST_LOSS_ACC]) + gsum[ORP_FIT_MAX_PARAMS];
+        const double cnt_acc = ((flags & 1) ? 0.0 : state[ST_COUNT_ACC]) + gsum[ORP_FIT_MAX_PARAMS + 1];
+        state[ST_LOSS_ACC] = loss_acc;
+        state[ST_COUNT_ACC] = cnt_acc;
+        if (flags & 2) epoch_end(P, params, state, loss_acc / cnt_acc);
+    }
+}
+
+__global__ void fit_update_kernel(int P, float* __restrict__ params, double* __restrict__ state,
+                                  const double* __restrict__ gsum, int flags) {
+    if (state[ST_STOP] != 0.0) return;
+    optimiser_step(P, params, state, gsum, flags);
+}
+
+// Fixed-order sum of the per-block partials by ONE block of 256 threads: lane l adds blocks l, l+32, ... in
+// increasing order, then a shuffle tree combines the 32 lane sums — the same association on every launch,
+// whichever block finished last.  Writes gsum and (optionally) a shared-memory copy.
+__device__ __forceinline__ void reduce_partials(const double* __restrict__ partials, int n_blocks,
+                                                double* __restrict__ gsum, double* s_copy) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int k = warp; k < kGsumLen; k += 8) {
+        double t = 0.0;
+        for (int b = lane; b < n_blocks; b += 32) t += __ldcg(partials + (size_t)b * kGsumLen + k);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+        if (lane == 0) { gsum[k] = t; if (s_copy) s_copy[k] = t; }
+    }
+}
+
 constexpr int kFitThreads = 256;
-constexpr int kGsum = ORP_FIT_MAX_PARAMS + 2;      // grads, loss sum, count
+constexpr int kGsum = kGsumLen;
 
 template <int NET>
 __device__ __forceinline__ void block_reduce_to(const Grads<NET>& g, float loss, uint32_t n, double* __restrict__ dst) {
@@ -321,16 +469,21 @@ __device__ __forceinline__ void unpack_raw(const FitArgs& a, const RawSample<NET
 }
 
 // A block walks tiles of kFitThreads * U consecutive samples (thread t owns samples t, t + 256, ... of the
-// tile: every load is a full-line warp access).  The loads of the NEXT tile are issued before the arithmetic
-// of the current one, so their HBM latency hides behind U x ~250 issue slots per warp: at 8 warps per SM
-// (the 97/122 gradient accumulators take the register file) there is no other warp to switch to.
+// tile: every load is a full-line warp access) and pushes them through the network two at a time.  The loads
+// of the NEXT tile are issued before the arithmetic of the current one, so their HBM latency hides behind
+// U x ~230 issue slots per warp: at 8 warps per SM (the 97/122 gradient accumulators take the register file)
+// there is no other warp to switch to.
+constexpr int kFitS = 2;                                   // samples per thread in flight through the network
 template <int NET> constexpr int kFitUnroll = NET == ORP_NET_EO ? 4 : 2;
 
-template <int NET, int LOSS, typename T>
-__global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, const float* __restrict__ params,
-                                                               const double* __restrict__ state, double* __restrict__ partials) {
+// STEP = true: the whole optimiser step in this one launch — the block that arrives last (a ticket counter in
+// the state block) adds the partials in the same fixed order as fit_reduce_kernel and applies the update.
+template <int NET, int LOSS, typename T, bool STEP>
+__global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, float* params, double* state,
+                                                               double* __restrict__ partials, double* __restrict__ gsum, int flags) {
     using N = Net<NET>;
-    constexpr int U = kFitUnroll<NET>;
+    constexpr int U = kFitUnroll<NET>, S = kFitS;
+    static_assert(U % S == 0, "tile slots are consumed S at a time");
     if (state[ST_STOP] != 0.0) return;
     __shared__ __align__(16) float s_w[kSmemW];
     load_weights<NET>(s_w, params, threadIdx.x, kFitThreads);
@@ -357,102 +510,50 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
             if (nb + (uint64_t)u * kFitThreads < a.count) load_raw<NET, T>(a, nb + (uint64_t)u * kFitThreads, nxt[u]);
         }
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            if (base + (uint64_t)u * kFitThreads < a.count) {
-                float x[N::IN], s_t1, phi, psi, l, dv;
-                Acts<NET> act;
-                unpack_raw<NET, T>(a, cur[u], x, s_t1);
-                const float v = net_forward<NET>(s_wa, x, s_t1, a.b_t1, act, phi, psi);
-                loss_grad<LOSS>(cur[u].y, v, l, dv);
-                loss += l;
-                net_backward<NET>(s_wa, x, s_t1, a.b_t1, dv, act, g);
-                ++n;
+        for (int u = 0; u < U; u += S) {
+            if (base + (uint64_t)u * kFitThreads < a.count) {                 // slot u valid; later slots of the group may not be
+                float x[S][N::IN], s_t1[S], phi[S], psi[S], v[S], dv[S];
+                Acts<NET, S> act;
+#pragma unroll
+                for (int s = 0; s < S; ++s) unpack_raw<NET, T>(a, cur[u + s], x[s], s_t1[s]);      // out-of-range slots hold zeros
+                net_forward<NET, S>(s_wa, x, s_t1, a.b_t1, act, phi, psi, v);
+#pragma unroll
+                for (int s = 0; s < S; ++s) {
+                    const bool ok = base + (uint64_t)(u + s) * kFitThreads < a.count;
+                    float l;
+                    loss_grad<LOSS>(cur[u + s].y, v[s], l, dv[s]);
+                    if (!ok) { l = 0.f; dv[s] = 0.f; }
+                    loss += l;
+                    n += ok ? 1u : 0u;
+                }
+                net_backward<NET, S>(s_wa, x, s_t1, a.b_t1, dv, act, g);
             }
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) cur[u] = nxt[u];
     }
     block_reduce_to<NET>(g, loss, n, partials + (size_t)blockIdx.x * kGsum);
+    if (STEP) {
+        __shared__ bool s_last;
+        __shared__ double s_g[kGsumLen];
+        unsigned int* ticket = reinterpret_cast<unsigned int*>(state + ST_TICKET);
+        __threadfence();                                   // this block's partial is visible before its ticket
+        __syncthreads();
+        if (threadIdx.x == 0) s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+        __syncthreads();
+        if (!s_last) return;
+        __threadfence();
+        reduce_partials(partials, (int)gridDim.x, gsum, s_g);
+        __syncthreads();
+        optimiser_step(N::P, params, state, s_g, flags);
+        if (threadIdx.x == 0) *ticket = 0u;                // ready for the next launch
+    }
 }
 
-// Fixed-order sum of the per-block partials: lane l adds blocks l, l+32, ... in increasing order, then a
-// shuffle tree combines the 32 lane sums — the same association on every launch, whichever block finished last.
 __global__ void __launch_bounds__(256) fit_reduce_kernel(const double* __restrict__ partials, int n_blocks,
                                                          const double* __restrict__ state, double* __restrict__ gsum) {
     if (state[ST_STOP] != 0.0) return;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int k = warp; k < kGsum; k += 8) {
-        double t = 0.0;
-        for (int b = lane; b < n_blocks; b += 32) t += partials[(size_t)b * kGsum + k];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
-        if (lane == 0) gsum[k] = t;
-    }
-}
-
-__device__ __forceinline__ double schedule_lr(int epoch, double lr) {      // Replicating_Portfolio.py:128-136
-    if (epoch < 100) return 1e-2;
-    if (epoch < 200) return 1e-3;
-    if (epoch < 400) return 5e-4;
-    return lr;
-}
-
-// Adam (Keras: lr_t = lr sqrt(1-b2^t)/(1-b1^t); w -= lr_t m / (sqrt(v) + 1e-7)), fp32 like the Keras variables.
-__device__ __forceinline__ void adam_apply(float* __restrict__ params, double* __restrict__ state, int k, float grad,
-                                           float lr_t) {
-    float m = (float)state[ST_ADAM_M + k], v = (float)state[ST_ADAM_V + k];
-    m = 0.9f * m + (1.f - 0.9f) * grad;
-    v = 0.999f * v + (1.f - 0.999f) * grad * grad;
-    state[ST_ADAM_M + k] = m;
-    state[ST_ADAM_V + k] = v;
-    params[k] -= lr_t * m / (sqrtf(v) + 1e-7f);
-}
-
-// End-of-epoch callbacks, run by ONE thread after the epoch's updates are visible in params.
-__device__ void epoch_end(int P, const float* __restrict__ params, double* __restrict__ state, double cur) {
-    state[ST_LAST_LOSS] = cur;
-    int epoch = (int)state[ST_EPOCH];
-    double wait = state[ST_WAIT] + 1.0;
-    if (cur < state[ST_BEST]) {                       // EarlyStopping(monitor='loss', min_delta=0)
-        state[ST_BEST] = cur;
-        wait = 0.0;
-        for (int k = 0; k < P; ++k) state[ST_BEST_W + k] = params[k];     // restore_best_weights=True
-        state[ST_HAVE_BEST] = 1.0;
-    }
-    state[ST_WAIT] = wait;
-    if (wait >= state[ST_PATIENCE] && epoch > 0) { state[ST_STOP] = 1.0; state[ST_STOPPED_EARLY] = 1.0; }
-    epoch += 1;
-    state[ST_EPOCH] = epoch;
-    state[ST_EPOCHS_RUN] = epoch;
-    state[ST_TOTAL_EPOCHS] += 1.0;
-    if (epoch >= (int)state[ST_EPOCHS]) state[ST_STOP] = 1.0;
-}
-
-// One optimiser step.  flags bit 0: first batch of the epoch (LearningRateScheduler.on_epoch_begin),
-// bit 1: last batch (epoch loss = sample-weighted mean of the batch losses, then the callbacks).
-__global__ void fit_update_kernel(int P, float* __restrict__ params, double* __restrict__ state,
-                                  const double* __restrict__ gsum, int flags) {
-    if (state[ST_STOP] != 0.0) return;
-    __shared__ float s_lr_t;
-    if (threadIdx.x == 0) {
-        double lr = state[ST_LR];
-        if ((flags & 1) && state[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)state[ST_EPOCH], lr);
-        state[ST_LR] = lr;
-        const double t = state[ST_ADAM_T] + 1.0;
-        state[ST_ADAM_T] = t;
-        s_lr_t = (float)(lr * sqrt(1.0 - pow(0.999, t)) / (1.0 - pow(0.9, t)));
-    }
-    __syncthreads();
-    const double inv_n = 1.0 / gsum[ORP_FIT_MAX_PARAMS + 1];
-    if (threadIdx.x < P) adam_apply(params, state, threadIdx.x, (float)(gsum[threadIdx.x] * inv_n), s_lr_t);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        const double loss_acc = ((flags & 1) ? 0.0 : state[ST_LOSS_ACC]) + gsum[ORP_FIT_MAX_PARAMS];
-        const double cnt_acc = ((flags & 1) ? 0.0 : state[ST_COUNT_ACC]) + gsum[ORP_FIT_MAX_PARAMS + 1];
-        state[ST_LOSS_ACC] = loss_acc;
-        state[ST_COUNT_ACC] = cnt_acc;
-        if (flags & 2) epoch_end(P, params, state, loss_acc / cnt_acc);
-    }
+    reduce_partials(partials, n_blocks, gsum, nullptr);
 }
 
 __global__ void fit_init_kernel(double* __restrict__ state) {
@@ -485,16 +586,30 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitAr
     __syncthreads();
     const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
     double sv = 0.0, sphi = 0.0, spsi = 0.0, sae = 0.0;
-    for (uint64_t i = (uint64_t)blockIdx.x * kFitThreads + threadIdx.x; i < a.count; i += (uint64_t)gridDim.x * kFitThreads) {
-        float x[N::IN], s_t, s_t1, phi, psi;
-        Acts<NET> act;
-        load_sample<NET, T>(a, i, x, s_t, s_t1);
-        net_forward<NET>(s_wa, x, s_t, a.b_t, act, phi, psi);
-        const float v0 = fmaf(phi, s_t, psi * a.b_t);            // model.predict(X0): prices at t
-        const float v1 = fmaf(phi, s_t1, psi * a.b_t1);          // model.predict(X1): prices at t+1
-        if (values_out) values_out[i] = v0;
-        sv += v0; sphi += phi; spsi += psi;
-        if (a.target) sae += fabsf(a.target[i] - v1);            // 'mae' metric of model.evaluate(X1, ...)
+    constexpr int S = 1;                                   // memory-bound: occupancy (64 registers) beats weight reuse here
+    const uint64_t stride = (uint64_t)gridDim.x * kFitThreads;
+    for (uint64_t i = (uint64_t)blockIdx.x * kFitThreads + threadIdx.x; i < a.count; i += S * stride) {
+        float x[S][N::IN], s_t[S], s_t1[S], phi[S], psi[S], v0[S];
+        Acts<NET, S> act;
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const uint64_t is = i + s * stride;
+#pragma unroll
+            for (int q = 0; q < N::IN; ++q) x[s][q] = 0.f;
+            s_t[s] = s_t1[s] = 0.f;
+            if (is < a.count) load_sample<NET, T>(a, is, x[s], s_t[s], s_t1[s]);
+        }
+        net_forward<NET, S>(s_wa, x, s_t, a.b_t, act, phi, psi, v0);          // model.predict(X0): prices at t
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const uint64_t is = i + s * stride;
+            if (is < a.count) {
+                const float v1 = fmaf(phi[s], s_t1[s], psi[s] * a.b_t1);      // model.predict(X1): prices at t+1
+                if (values_out) values_out[is] = v0[s];
+                sv += v0[s]; sphi += phi[s]; spsi += psi[s];
+                if (a.target) sae += fabsf(a.target[is] - v1);                // 'mae' metric of model.evaluate(X1, ...)
+            }
+        }
     }
     __shared__ double s_red[kFitThreads / 32][4];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -571,13 +686,13 @@ __global__ void __launch_bounds__(kMiniThreads, 1) fit_minibatch_kernel(const Fi
             // position b0 + r of the epoch's permutation (cycle-walk down from the enclosing power of two)
             uint64_t i = perm_pow2(b0 + r, bits, epoch_seed);
             while (i >= a.count) i = perm_pow2(i, bits, epoch_seed);
-            float x[N::IN], s_t_, s_t1, phi, psi, l, dv;
-            Acts<NET> act;
-            load_sample<NET, T>(a, i, x, s_t_, s_t1);
-            const float vv = net_forward<NET>(s_wa, x, s_t1, a.b_t1, act, phi, psi);
-            loss_grad<LOSS>(a.target[i], vv, l, dv);
+            float x[1][N::IN], s_t_, s_t1[1], phi[1], psi[1], vv[1], l, dv[1];
+            Acts<NET, 1> act;
+            load_sample<NET, T>(a, i, x[0], s_t_, s_t1[0]);
+            net_forward<NET, 1>(s_wa, x, s_t1, a.b_t1, act, phi, psi, vv);
+            loss_grad<LOSS>(a.target[i], vv[0], l, dv[0]);
             loss += l;
-            net_backward<NET>(s_wa, x, s_t1, a.b_t1, dv, act, g);
+            net_backward<NET, 1>(s_wa, x, s_t1, a.b_t1, dv, act, g);
         }
 #pragma unroll
         for (int k = 0; k < N::P; ++k) {
@@ -675,12 +790,45 @@ extern "C" int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const
     cudaStream_t st = (cudaStream_t)stream;
     const int grid = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
     double* partials = reinterpret_cast<double*>(d_scratch);
-#define CALL_GRAD(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T><<<grid, kFitThreads, 0, st>>>(a, d_params, d_state, partials)
+#define CALL_GRAD(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, false><<<grid, kFitThreads, 0, st>>>(a, const_cast<float*>(d_params), const_cast<double*>(d_state), partials, d_gsum, 0)
     ORP_FIT_DISPATCH(CALL_GRAD);
 #undef CALL_GRAD
     ORP_LAUNCH_CHECK("fit_grad_kernel");
     fit_reduce_kernel<<<1, 256, 0, st>>>(partials, grid, d_state, d_gsum);
     ORP_LAUNCH_CHECK("fit_reduce_kernel");
+    return ORP_OK;
+}
+
+static int fit_step_launch(const orp_fit_batch* b, float* d_params, double* d_state, double* d_gsum, void* d_scratch,
+                           int flags, cudaStream_t st) {
+    FitArgs a;
+    int rc = make_args(b, a, true);
+    if (rc) return rc;
+    const int grid = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
+    double* partials = reinterpret_cast<double*>(d_scratch);
+#define CALL_STEP(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, true><<<grid, kFitThreads, 0, st>>>(a, d_params, d_state, partials, d_gsum, flags)
+    ORP_FIT_DISPATCH(CALL_STEP);
+#undef CALL_STEP
+    ORP_LAUNCH_CHECK("fit_grad_kernel (single-launch step)");
+    return ORP_OK;
+}
+
+extern "C" int orp_fit_step(const orp_fit_batch* b, float* d_params, double* d_state, double* d_gsum, void* d_scratch,
+                            int flags, void* stream) {
+    ORP_REQUIRE(d_params && d_state && d_gsum && d_scratch, "null pointer");
+    return fit_step_launch(b, d_params, d_state, d_gsum, d_scratch, flags, (cudaStream_t)stream);
+}
+
+extern "C" int orp_fit_epochs(const orp_fit_batch* parts, int n_parts, float* d_params, double* d_state, double* d_gsum,
+                              void* d_scratch, int n_epochs, void* stream) {
+    ORP_REQUIRE(parts && d_params && d_state && d_gsum && d_scratch, "null pointer");
+    ORP_REQUIRE(n_parts >= 1 && n_epochs >= 0, "n_parts must be >= 1 and n_epochs >= 0");
+    for (int e = 0; e < n_epochs; ++e)
+        for (int k = 0; k < n_parts; ++k) {
+            const int flags = (k == 0 ? ORP_FIT_EPOCH_FIRST : 0) | (k == n_parts - 1 ? ORP_FIT_EPOCH_LAST : 0);
+            int rc = fit_step_launch(parts + k, d_params, d_state, d_gsum, d_scratch, flags, (cudaStream_t)stream);
+            if (rc) return rc;
+        }
     return ORP_OK;
 }
 

@@ -127,13 +127,36 @@ __device__ __forceinline__ void advance(const PathArgs& a, double& s_0, double& 
     }
 }
 
+__device__ __forceinline__ uint2 lds_u32x2(uint32_t saddr) {
+    uint2 r;
+    asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(r.x), "=r"(r.y) : "r"(saddr));
+    return r;
+}
+
+// Bytes of one engine's lane table in shared memory (one spare row: the loop prefetches one step ahead).
+__host__ __device__ inline size_t tlane_smem_bytes(int n_steps) { return (size_t)(n_steps + 2) * 256; }
+
 // FUSED (log-Euler GBM only): the table is transformed so that one Horner chain yields exp(drift + vol z);
 // the state is then the price itself, S_t = S_{t-1} * factor — no exp, no separate normal.
-template <int MODEL, typename OutT, bool FUSED>
+// TLS: the lane tables (256 B per dimension and engine) are staged in shared memory behind the coefficient table
+// when they fit (D <= ~300 for two engines); otherwise they are read through L1.
+// ALL: keep_every == 1, every step is stored (no keep test in the loop).
+template <int MODEL, typename OutT, bool FUSED, bool TLS, bool ALL>
 __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a) {
     static_assert(!FUSED || MODEL == ORP_MODEL_GBM_LOG, "only the log-Euler GBM step fuses into the table");
     extern __shared__ __align__(128) char s_tab[];
     load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
+    const int D = a.n_steps;
+    if (TLS) {
+        // rows 0 .. D of each engine's table, plus one zero row
+        uint2* dst_a = reinterpret_cast<uint2*>(s_tab + kNdtriTableBytes);
+        const int n = (D + 1) * 32;
+        for (int i = threadIdx.x; i < n + 32; i += blockDim.x) dst_a[i] = i < n ? __ldg(a.tlane_a + i) : make_uint2(0u, 0u);
+        if (MODEL == ORP_MODEL_SV) {
+            uint2* dst_b = reinterpret_cast<uint2*>(s_tab + kNdtriTableBytes + tlane_smem_bytes(D));
+            for (int i = threadIdx.x; i < n + 32; i += blockDim.x) dst_b[i] = i < n ? __ldg(a.tlane_b + i) : make_uint2(0u, 0u);
+        }
+    }
     __syncthreads();
     if (FUSED) {
         fuse_gbm_table(s_tab, a.c_drift, a.c_vol, threadIdx.x, blockDim.x);
@@ -142,11 +165,12 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
 
     const uint32_t tab = (uint32_t)__cvta_generic_to_shared(s_tab);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tls_a = tab + kNdtriTableBytes + lane * 8u;
+    const uint32_t tls_b = tls_a + (uint32_t)tlane_smem_bytes(D);
     constexpr int kWarps = kPathThreads / 32;
     const uint64_t end = a.start + a.count;
     const uint64_t w_first = a.start / kWarpPaths, w_last = (end - 1) / kWarpPaths;
     const uint64_t n_tiles = w_last - w_first + 1;
-    const int D = a.n_steps;
 
     // block-contiguous tiling: the 32 warps of a block work on 2048 consecutive paths
     for (uint64_t tile = (uint64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (uint64_t)gridDim.x * kWarps) {
@@ -171,12 +195,17 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
                 if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, a.dpad, my_dim, w);
             }
             const int nc = min(32, D - t0 + 1);
-            uint2 tl_next = __ldg(a.tlane_a + (size_t)t0 * 32 + lane);
+            // lane-table entries are fetched one step ahead: their latency hides behind the current step
+            uint32_t tp_a = tls_a + (uint32_t)t0 * 256u, tp_b = tls_b + (uint32_t)t0 * 256u;
+            uint2 tl_next = TLS ? lds_u32x2(tp_a) : __ldg(a.tlane_a + (size_t)t0 * 32 + lane);
+            uint2 tb_next = make_uint2(0u, 0u);
+            if (MODEL == ORP_MODEL_SV) tb_next = TLS ? lds_u32x2(tp_b) : __ldg(a.tlane_b + (size_t)t0 * 32 + lane);
             for (int s = 0; s < nc; ++s) {
                 const int t = t0 + s;
                 const uint32_t base = __shfl_sync(kFull, bl_a, s);
-                const uint2 tl = tl_next;                   // fetched one step ahead: its L1 latency hides behind this step
-                tl_next = __ldg(a.tlane_a + (size_t)min(t + 1, D) * 32 + lane);
+                const uint2 tl = tl_next;
+                if (TLS) { tp_a += 256u; tl_next = lds_u32x2(tp_a); }                      // row D + 1 exists (zeros)
+                else tl_next = __ldg(a.tlane_a + (size_t)min(t + 1, D) * 32 + lane);
                 if (FUSED) {
                     // exp(-inf) = 0 at the exact-zero coordinate, like np.exp of the reference's -inf log-price
                     s_0 *= table_eval(base ^ tl.x, tab);
@@ -187,19 +216,21 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
                     double y0 = 0.0, y1 = 0.0;
                     if (MODEL == ORP_MODEL_SV) {
                         const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
-                        const uint2 tb = __ldg(a.tlane_b + (size_t)t * 32 + lane);
+                        const uint2 tb = tb_next;
+                        if (TLS) { tp_b += 256u; tb_next = lds_u32x2(tp_b); }
+                        else tb_next = __ldg(a.tlane_b + (size_t)min(t + 1, D) * 32 + lane);
                         y0 = ndtri_bits(base_b ^ tb.x, tab);
                         y1 = ndtri_bits(base_b ^ tb.y, tab);
                     }
                     advance<MODEL>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
                 }
-                if (t == next_keep) {
+                if (ALL || t == next_keep) {
                     double o0 = s_0, o1 = s_1;
                     if (!kLevel<MODEL> && !FUSED) { o0 = exp(s_0); o1 = exp(s_1); }
                     optr += a.ld;
                     if (ok0) optr[0] = (OutT)o0;
                     if (ok1) optr[32] = (OutT)o1;
-                    next_keep += a.keep_every;
+                    if (!ALL) next_keep += a.keep_every;
                 }
             }
         }
@@ -300,25 +331,35 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
 }
 
 template <typename K>
-static int set_table_smem(K kernel) {
-    static bool done[64] = {false};
-    int dev = 0;
-    ORP_CUDA(cudaGetDevice(&dev));
-    (void)done;
-    ORP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kNdtriTableBytes));
+static int set_table_smem(K kernel, size_t bytes = kNdtriTableBytes) {
+    ORP_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return ORP_OK;
+}
+
+constexpr size_t kMaxDynSmem = 227 * 1024;       // per-block opt-in limit on sm_100
+
+template <int MODEL, typename OutT, bool FUSED, bool TLS, bool ALL>
+static int launch_paths_v(const PathArgs& a, size_t smem, cudaStream_t st) {
+    int rc = set_table_smem(paths_kernel<MODEL, OutT, FUSED, TLS, ALL>, smem);
+    if (rc) return rc;
+    const uint64_t n_tiles = (a.start + a.count - 1) / kWarpPaths - a.start / kWarpPaths + 1;
+    const uint64_t want = (n_tiles + 31) / 32;
+    const int grid = (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
+    paths_kernel<MODEL, OutT, FUSED, TLS, ALL><<<grid, kPathThreads, smem, st>>>(a);
+    ORP_LAUNCH_CHECK("paths_kernel");
     return ORP_OK;
 }
 
 template <int MODEL, typename OutT, bool FUSED = false>
 static int launch_paths(const PathArgs& a, cudaStream_t st) {
-    int rc = set_table_smem(paths_kernel<MODEL, OutT, FUSED>);
-    if (rc) return rc;
-    const uint64_t n_tiles = (a.start + a.count - 1) / kWarpPaths - a.start / kWarpPaths + 1;
-    const uint64_t want = (n_tiles + 31) / 32;
-    const int grid = (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
-    paths_kernel<MODEL, OutT, FUSED><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a);
-    ORP_LAUNCH_CHECK("paths_kernel");
-    return ORP_OK;
+    const size_t engines = MODEL == ORP_MODEL_SV ? 2 : 1;
+    const size_t with_tl = kNdtriTableBytes + engines * tlane_smem_bytes(a.n_steps);
+    const bool tls = with_tl <= kMaxDynSmem && !getenv("ORP_B200_NO_TLS");
+    const bool all = a.keep_every == 1;
+    if (tls) return all ? launch_paths_v<MODEL, OutT, FUSED, true, true>(a, with_tl, st)
+                        : launch_paths_v<MODEL, OutT, FUSED, true, false>(a, with_tl, st);
+    return all ? launch_paths_v<MODEL, OutT, FUSED, false, true>(a, kNdtriTableBytes, st)
+               : launch_paths_v<MODEL, OutT, FUSED, false, false>(a, kNdtriTableBytes, st);
 }
 
 

@@ -68,6 +68,8 @@ PROTOTYPES = {
     "orp_fit_scratch_bytes": (C.c_uint64, []),
     "orp_fit_grad": (C.c_int, [C.POINTER(FitBatch), _vp, _vp, _vp, _vp, _vp]),
     "orp_fit_update": (C.c_int, [_i32, _vp, _vp, _vp, _i32, _vp]),
+    "orp_fit_step": (C.c_int, [C.POINTER(FitBatch), _vp, _vp, _vp, _vp, _i32, _vp]),
+    "orp_fit_epochs": (C.c_int, [C.POINTER(FitBatch), _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "orp_fit_begin": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
     "orp_fit_init": (C.c_int, [_vp, _vp]),
     "orp_fit_end": (C.c_int, [_i32, _vp, _vp, _vp]),

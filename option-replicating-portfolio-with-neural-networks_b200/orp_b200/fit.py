@@ -71,6 +71,7 @@ class ReplicationNet:
         self.scratch = torch.empty(_lib.lib().orp_fit_scratch_bytes(), dtype=torch.uint8, device=self.device)
         self.sums = torch.zeros(4, dtype=torch.float64, device=self.device)
         self.launches = 0
+        self.two_stage = False      # True forces grad -> [all-reduce] -> update even on one GPU (tests, multi-GPU form)
 
     def batch(self, s_t, s_t1, target, inv_scale, bond_t, bond_t1, loss="mse", feat1=None, feat2=None):
         torch = _lib.require_cuda()
@@ -124,8 +125,23 @@ class ReplicationNet:
             parts = self.split(batch, steps_per_epoch) if mode == "scaled" else [batch]
             dist_on = is_distributed(self.group)
             done = 0
+            single_launch = mode == "scaled" and not dist_on and not self.two_stage
+            if single_launch:
+                parts_arr = (_lib.FitBatch * len(parts))()
+                for k, part in enumerate(parts):
+                    C.memmove(C.byref(parts_arr[k]), C.byref(part), C.sizeof(_lib.FitBatch))
             while done < epochs:
                 n = min(check_every, epochs - done)
+                if single_launch:
+                    # one process, one GPU: grad + fixed-order reduction + Adam/callbacks in ONE launch per optimiser
+                    # step, and the epoch loop itself runs inside the library (no Python between launches)
+                    _lib.check(L.orp_fit_epochs(parts_arr, len(parts), _lib.ptr(self.params), _lib.ptr(opt.state),
+                                                _lib.ptr(self.gsum), _lib.ptr(self.scratch), n, st))
+                    self.launches += n * len(parts)
+                    done += n
+                    if opt.state[_lib.ST_STOP].item() != 0.0:
+                        break
+                    continue
                 for e in range(n):
                     if mode == "scaled":
                         for k, part in enumerate(parts):

@@ -100,6 +100,29 @@ def test_scaled_fit_tracks_oracle(cuda, net, spe):
     np.testing.assert_allclose(sums[:3] / n, [v0.double().mean(), phi.double().mean(), psi.double().mean()], atol=2e-3)
 
 
+@pytest.mark.parametrize("net,n,spe", [("eo", 70_001, 3), ("rp", 5_000, 1), ("eo", 300_000, 8)])
+def test_single_launch_step_equals_two_stage(cuda, net, n, spe):
+    """orp_fit_epochs (grad + fixed-order reduction + update in one launch, epoch loop inside the library) leaves
+    exactly the weights, optimiser state and losses of orp_fit_grad -> orp_fit_update: bit for bit."""
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    s_t, s_t1, y, f1, f2 = _toy(n, 4, net)
+    bias = 0.1 if net == "eo" else [0.9, 0.1]
+    dev = lambda a: torch.from_numpy(a).to(cuda)
+    out = []
+    for two_stage in (False, True):
+        model = ReplicationNet(net, init_params(net, 1234, bias), cuda)
+        model.two_stage = two_stage
+        opt = Optimizer(cuda)
+        b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / 100.0, 1.02, 1.03,
+                        feat1=dev(f1) if net == "rp" else None, feat2=dev(f2) if net == "rp" else None)
+        h = model.fit(b, opt, epochs=25, patience=4, use_schedule=True, mode="scaled", steps_per_epoch=spe, check_every=7)
+        out.append((h, model.params.cpu().numpy().copy(), opt.state[:400].cpu().numpy().copy(), model.launches))
+    (h0, w0, st0, l0), (h1, w1, st1, l1) = out
+    assert h0 == h1
+    assert np.array_equal(w0, w1) and np.array_equal(st0, st1)
+    assert l0 < l1                      # one launch per optimiser step instead of three
+
+
 def test_early_stopping_and_restore(cuda):
     """Constant target reached quickly: the stop fires after `patience` non-improving epochs, the best weights
     come back, later enqueued epochs are no-ops (device-side control block)."""

@@ -1,6 +1,7 @@
 """GPU parity tests (through the C ABI): Sobol points bit-exact, inverse normal, paths, payoff sums.
-Tolerances: integer points bit-exact; normals 8e-15 relative-or-absolute against scipy.special.ndtri;
-fp64 path values 1e-6 relative (north_star; observed ~1e-13), fp32 1e-4; sums 1e-9 relative."""
+Tolerances: integer points bit-exact; normals 2e-11 relative-or-absolute against scipy.special.ndtri (the 32-byte-row
+table is good to 9e-12, five orders inside what the paths need); fp64 path values 1e-6 relative (north_star;
+observed ~1e-11), fp32 1e-4; sums 1e-9 relative."""
 import json
 import os
 
@@ -77,14 +78,14 @@ def test_ndtri_matches_scipy(cuda):
     fin = np.isfinite(ref)
     assert np.array_equal(fin, np.isfinite(z))
     err = np.abs(z[fin] - ref[fin]) / np.maximum(1.0, np.abs(ref[fin]))
-    assert err.max() < 8e-15, err.max()      # table: 4e-15 (fp32 tail of the Horner chain) + scipy: 4e-16
+    assert err.max() < 2e-11, err.max()      # table: 9e-12 (degree 5, c2..c5 in fp32: tools/gen_ndtri_table.py) + scipy: 4e-16
 
 
 def test_sobol_normal_matches_reference_call_form(cuda):
     import orp_b200
     w = orp_b200.sobol_normal(8, 13, 1235).cpu().numpy()
     ref = osobol.sobol_norm(8, 13, 1235)
-    np.testing.assert_allclose(w, ref, rtol=8e-15, atol=8e-15)
+    np.testing.assert_allclose(w, ref, rtol=2e-11, atol=2e-11)
 
 
 SIMS = {
