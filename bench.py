@@ -35,7 +35,9 @@ import numpy as np  # noqa: E402
 METRIC = "path-steps/sec"
 CFG = dict(S0=100.0, K=100.0, T=1.0, r=0.05, sigma=0.2, D=252)
 FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12     # SIMT fp32 FMA peak at max clock (not in MEASURED_PEAKS.json)
-FIT_FLOP_PER_SAMPLE = 2 * 315                             # 315 FMA-class ops per sample (EO net, fwd+bwd)
+FIT_FLOP_PER_SAMPLE = 2 * 232 + 56                        # 232 multiply-adds + 56 elementwise ops per sample (EO net, fwd+bwd)
+FIT_FMA_PIPE_SLOTS = 144 * 2                              # FMA-pipe issue cycles per warp-sample: 144 packed FFMA2/FMUL2/FADD2-class ops, 2 cycles each
+FIT_PEAK_SAMPLES_PER_S = 148 * 4 * 32 * 1.965e9 / FIT_FMA_PIPE_SLOTS     # what the FMA pipe allows at max clock
 
 
 def measured_peaks():
@@ -44,6 +46,19 @@ def measured_peaks():
             return json.load(f), "measured"
     except OSError:
         return {"hbm_gbs": 6650.0}, "fallback"
+
+
+def profiled_traffic(m, D):
+    """dram bytes (read + write) of one paths_kernel launch of THIS workload from the committed `ncu --set full`
+    summary (profiles/r01_paths_kernel_traffic.json), else None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_paths_kernel_traffic.json")) as f:
+            t = json.load(f)
+        if t.get("paths_log2") == m and t.get("path_steps") == D:
+            return t["dram_bytes_read"] + t["dram_bytes_write"]
+    except (OSError, KeyError, ValueError):
+        pass
+    return None
 
 
 class ClockSampler:
@@ -157,7 +172,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    cores = os.cpu_count() or 1
+    # The reference's fit is a serial chain of 512-sample Adam steps on 8-wide layers: intra-op threads only add
+    # overhead (measured on 8 cores: 27.7k path-steps/s with 8 torch threads against 104k with 1), so the arm runs
+    # the way the reference itself does, on one core, and says so.
+    cores = 1
     D = args.path_steps
     times = []
     for i in range(args.warmup + args.steps):
@@ -207,25 +225,29 @@ def run_own(args):
     for _ in range(args.warmup):
         last = pipe.step()
     sampler = ClockSampler(local)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     barrier()
     if rank == 0:
         sampler.start()
-    t0 = time.perf_counter()
+    ev[0].record()
     stages = []
     for _ in range(args.steps):
         last = pipe.step()
         stages.append(last)
+    ev[1].record()
     barrier()
-    elapsed = time.perf_counter() - t0
+    elapsed = ev[0].elapsed_time(ev[1]) * 1e-3                 # device time of exactly `steps` steps (CUDA events)
     clocks = sampler.stop() if rank == 0 else None
-    # end to end: host-side engine set-up + H2D of its tables + pipeline + D2H of the results, every step
+    # end to end through the public API: host-side engine set-up (NumPy bit stream + integer scramble) + H2D of its
+    # tables + pipeline + D2H of the results, every step
     barrier()
-    t1 = time.perf_counter()
     n_e2e = max(1, min(args.steps, 2))
+    ev[2].record()
     for _ in range(n_e2e):
         pipe.step(fresh_engine=True)
+    ev[3].record()
     barrier()
-    e2e_elapsed = (time.perf_counter() - t1) / n_e2e
+    e2e_elapsed = ev[2].elapsed_time(ev[3]) * 1e-3 / n_e2e
     tt = torch.tensor([elapsed, e2e_elapsed], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -254,10 +276,15 @@ def run_own(args):
         "config": {"workload": workload_name(m, D), "paths_log2": m, "path_steps": D, "parallelism": f"paths sharded x{world} by Sobol index range",
                    "l2": "inputs larger than L2 (the path array is read back by the fits; >= 16 GB per GPU)"},
         "roofline": {"kernel": "paths_kernel<GBM_LOG,double>", "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
-                     "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None, "peak_kind": peak_kind + " (burst copy figure)",
+                     "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": profiled_traffic(m, D) if world == 1 else None,
+                     "peak_kind": peak_kind + " (burst copy figure)",
                      "algorithmic_bytes_per_launch": path_bytes, "ms_per_launch": t_paths},
-        "fit_kernel": {"bound": "fp32 SIMT issue", "tflops": fit_flops / (t_fit * 1e-3) / 1e12, "peak_nominal_tflops": FP32_NOMINAL_TFLOPS,
-                       "epochs_per_step": epochs, "samples_per_s": 2 ** m / world * epochs / (t_fit * 1e-3)},
+        "fit_kernel": {"kernel": "fit_grad_kernel<EO,MSE,double,step>", "bound": "fp32 FMA pipe (packed FFMA2), not hbm/tensor: width-8 layers",
+                       "tflops": fit_flops / (t_fit * 1e-3) / 1e12, "peak_nominal_tflops": FP32_NOMINAL_TFLOPS,
+                       "epochs_per_step": epochs, "samples_per_s_per_gpu": 2 ** m / world * epochs / (t_fit * 1e-3),
+                       "fma_pipe_peak_samples_per_s": FIT_PEAK_SAMPLES_PER_S,
+                       "frac_of_fma_pipe": 2 ** m / world * epochs / (t_fit * 1e-3) / FIT_PEAK_SAMPLES_PER_S,
+                       "note": "whole fit stage incl. predict passes and launch gaps"},
         "stages_ms": {"paths": t_paths, "payoff": t_pay, "fit": t_fit},
         "path_stage_path_steps_per_s": total_steps / world / (t_paths * 1e-3) * world,
         "e2e": {"value": total_steps / e2e_elapsed, "unit": "path-steps/s", "h2d_bytes_per_step": int(eng.sv32.nbytes + eng.tlane.nbytes),
@@ -287,7 +314,7 @@ def main():
     ap.add_argument("--m", type=int, default=26, help="log2 of the total path count (BASELINE C5: 26)")
     ap.add_argument("--path-steps", type=int, default=CFG["D"], help="time steps per path (BASELINE C5: 252)")
     ap.add_argument("--cpu-sample-m", type=int, default=12)
-    ap.add_argument("--ref-sample-m", type=int, default=11)
+    ap.add_argument("--ref-sample-m", type=int, default=12)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     return run_reference(args) if args.impl == "reference" else run_own(args)
