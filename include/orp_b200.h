@@ -200,6 +200,15 @@ int orp_fit_step(const orp_fit_batch* b, float* d_params, double* d_state, doubl
 int orp_fit_epochs(const orp_fit_batch* parts, int n_parts, float* d_params, double* d_state, double* d_gsum,
                    void* d_scratch, int n_epochs, void* stream);
 
+/* The whole epoch loop of Model.fit (Replicating_Portfolio.py:211) in ONE cooperative launch, single GPU: the batch is
+ * cut into n_parts contiguous ranges of ceil(count / n_parts) samples (one optimiser step each); a grid of one thread
+ * block per SM stays resident, synchronises once per step with a grid barrier, and every block applies the same
+ * fixed-order reduction and Adam step to its own copy of the weights.  Runs at most n_epochs epochs and returns to
+ * the host as soon as EarlyStopping fires.  Results are bit-identical to orp_fit_grad -> orp_fit_update.
+ * Needs a device that supports cooperative launches (every B200 does). */
+int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
+                void* d_scratch, int n_epochs, void* stream);
+
 /* Starts a Model.fit call: resets the early-stopping state, keeps weights and Adam moments (they persist across
  * time steps, Replicating_Portfolio.py:203-211).  use_schedule = 1 for the first fit. */
 int orp_fit_begin(double* d_state, int epochs, int patience, int use_schedule, void* stream);

@@ -17,7 +17,9 @@ enum {
     ST_STOPPED_EARLY, ST_LAST_LOSS, ST_EPOCHS_RUN, ST_HAVE_BEST, ST_TOTAL_EPOCHS, ST_LOSS_ACC, ST_COUNT_ACC,
     ST_ADAM_M = 16, ST_ADAM_V = ST_ADAM_M + ORP_FIT_MAX_PARAMS, ST_BEST_W = ST_ADAM_V + ORP_FIT_MAX_PARAMS,
     ST_TICKET = ST_BEST_W + ORP_FIT_MAX_PARAMS,      // block-arrival counter of the single-launch step (used as uint32)
-    ST_END = ST_TICKET + 1
+    ST_BARRIER,                                      // persistent kernel: grid-barrier arrivals (uint32) | exits (uint32)
+    ST_ABORT,                                        // persistent kernel: non-zero when a grid barrier timed out (uint32)
+    ST_END
 };
 static_assert(ST_END <= ORP_FIT_STATE_DOUBLES, "state block too small");
 
@@ -303,8 +305,9 @@ __device__ __forceinline__ void net_backward(uint32_t w, const float (&x)[S][Net
 // per-sample loss and dLoss/dV (without the 1/N of the batch mean)
 template <int LOSS>
 __device__ __forceinline__ void loss_grad(float y, float v, float& l, float& dv) {
-    if (LOSS == ORP_LOSS_MSE) { const float e = v - y; l = e * e; dv = 2.f * e; }
-    else { const float e = y - v; l = fmaxf(0.99f * e, (0.99f - 1.f) * e); dv = e > 0.f ? -0.99f : 0.01f; }   // RP.py:138-142
+    // products rounded on their own: `loss += l` must not contract into an FMA in one kernel and not in another
+    if (LOSS == ORP_LOSS_MSE) { const float e = v - y; l = __fmul_rn(e, e); dv = 2.f * e; }
+    else { const float e = y - v; l = fmaxf(__fmul_rn(0.99f, e), __fmul_rn(0.99f - 1.f, e)); dv = e > 0.f ? -0.99f : 0.01f; }   // RP.py:138-142
 }
 
 struct FitArgs {
@@ -339,14 +342,21 @@ __device__ __forceinline__ double schedule_lr(int epoch, double lr) {      // Re
 }
 
 // Adam (Keras: lr_t = lr sqrt(1-b2^t)/(1-b1^t); w -= lr_t m / (sqrt(v) + 1e-7)), fp32 like the Keras variables.
+// Every operation is rounded on its own (no FMA contraction), so that the three drivers of a fit (two-stage,
+// single-launch step, persistent kernel) and the Keras-faithful mini-batch kernel produce the same bits.
+__device__ __forceinline__ void adam_core(float& m, float& v, float& w, float grad, float lr_t) {
+    m = __fadd_rn(__fmul_rn(0.9f, m), __fmul_rn(1.f - 0.9f, grad));
+    v = __fadd_rn(__fmul_rn(0.999f, v), __fmul_rn(1.f - 0.999f, __fmul_rn(grad, grad)));
+    w = __fsub_rn(w, __fdiv_rn(__fmul_rn(lr_t, m), __fadd_rn(__fsqrt_rn(v), 1e-7f)));
+}
+
 __device__ __forceinline__ void adam_apply(float* __restrict__ params, double* __restrict__ state, int k, float grad,
                                            float lr_t) {
-    float m = (float)state[ST_ADAM_M + k], v = (float)state[ST_ADAM_V + k];
-    m = 0.9f * m + (1.f - 0.9f) * grad;
-    v = 0.999f * v + (1.f - 0.999f) * grad * grad;
+    float m = (float)state[ST_ADAM_M + k], v = (float)state[ST_ADAM_V + k], w = params[k];
+    adam_core(m, v, w, grad, lr_t);
     state[ST_ADAM_M + k] = m;
     state[ST_ADAM_V + k] = v;
-    params[k] -= lr_t * m / (sqrtf(v) + 1e-7f);
+    params[k] = w;
 }
 
 // End-of-epoch callbacks, run by ONE thread after the epoch's updates are visible in params.
@@ -476,26 +486,16 @@ __device__ __forceinline__ void unpack_raw(const FitArgs& a, const RawSample<NET
 constexpr int kFitS = 2;                                   // samples per thread in flight through the network
 template <int NET> constexpr int kFitUnroll = NET == ORP_NET_EO ? 4 : 2;
 
-// STEP = true: the whole optimiser step in this one launch — the block that arrives last (a ticket counter in
-// the state block) adds the partials in the same fixed order as fit_reduce_kernel and applies the update.
-template <int NET, int LOSS, typename T, bool STEP>
-__global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, float* params, double* state,
-                                                               double* __restrict__ partials, double* __restrict__ gsum, int flags) {
+// Forward + backward over this block's tiles of one batch: block `block` of `n_blocks` takes tiles block,
+// block + n_blocks, ...  Adds into g / loss / n.
+template <int NET, int LOSS, typename T>
+__device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa, uint32_t block, uint32_t n_blocks,
+                                                 Grads<NET>& g, float& loss, uint32_t& n) {
     using N = Net<NET>;
     constexpr int U = kFitUnroll<NET>, S = kFitS;
     static_assert(U % S == 0, "tile slots are consumed S at a time");
-    if (state[ST_STOP] != 0.0) return;
-    __shared__ __align__(16) float s_w[kSmemW];
-    load_weights<NET>(s_w, params, threadIdx.x, kFitThreads);
-    __syncthreads();
-    const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
-
-    Grads<NET> g;
-    g.zero();
-    float loss = 0.f;
-    uint32_t n = 0;
-    const uint64_t tile = (uint64_t)kFitThreads * U, stride = (uint64_t)gridDim.x * tile;
-    uint64_t base = (uint64_t)blockIdx.x * tile + threadIdx.x;
+    const uint64_t tile = (uint64_t)kFitThreads * U, stride = (uint64_t)n_blocks * tile;
+    uint64_t base = (uint64_t)block * tile + threadIdx.x;
     RawSample<NET, T> cur[U], nxt[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -532,6 +532,25 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
 #pragma unroll
         for (int u = 0; u < U; ++u) cur[u] = nxt[u];
     }
+}
+
+// STEP = true: the whole optimiser step in this one launch — the block that arrives last (a ticket counter in
+// the state block) adds the partials in the same fixed order as fit_reduce_kernel and applies the update.
+template <int NET, int LOSS, typename T, bool STEP>
+__global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, float* params, double* state,
+                                                               double* __restrict__ partials, double* __restrict__ gsum, int flags) {
+    using N = Net<NET>;
+    if (state[ST_STOP] != 0.0) return;
+    __shared__ __align__(16) float s_w[kSmemW];
+    load_weights<NET>(s_w, params, threadIdx.x, kFitThreads);
+    __syncthreads();
+    const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
+
+    Grads<NET> g;
+    g.zero();
+    float loss = 0.f;
+    uint32_t n = 0;
+    accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, gridDim.x, g, loss, n);
     block_reduce_to<NET>(g, loss, n, partials + (size_t)blockIdx.x * kGsum);
     if (STEP) {
         __shared__ bool s_last;
@@ -574,6 +593,207 @@ __global__ void fit_end_kernel(int P, float* __restrict__ params, double* __rest
     if (state[ST_STOPPED_EARLY] != 0.0 && state[ST_HAVE_BEST] != 0.0 && threadIdx.x < P)
         params[threadIdx.x] = (float)state[ST_BEST_W + threadIdx.x];
     if (threadIdx.x == 0) state[ST_STOP] = 1.0;
+}
+
+// ---- persistent fit: every epoch of a Model.fit call in ONE cooperative launch ----------------------
+//
+// One block per SM stays resident for the whole fit.  Per optimiser step: each block accumulates its tiles of the
+// batch, reduces to one fp64 partial (stored [parity][k][block], so the cross-block read is coalesced), passes
+// a grid barrier, then EVERY block adds the partials in the same fixed order and applies the Adam step to its own
+// shared-memory copy of the weights (moments in registers, callback state in shared memory): all blocks hold
+// bit-identical weights and take identical decisions, so no second barrier and no weight round trip through
+// global memory are needed.  Block 0 writes weights and state back when the fit stops or the epochs run out.
+// Per-step fixed cost: one block reduction + one barrier (~2 us) instead of a kernel boundary (~18 us measured).
+__device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// All threads of all blocks call.  Returns false when the barrier timed out (a block is missing: the launch was
+// not cooperative, or the device is wedged) — every block then leaves the kernel instead of hanging the GPU.
+__device__ __forceinline__ bool grid_barrier(unsigned int* arrivals, unsigned int* abort_flag, unsigned int target) {
+    __shared__ int s_ok;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(arrivals, 1u);
+        int ok = 1;
+        unsigned int spins = 0;
+        while (ld_acquire_u32(arrivals) < target) {
+            if (++spins > (1u << 26) || ld_acquire_u32(abort_flag) != 0u) { atomicExch(abort_flag, 1u); ok = 0; break; }
+        }
+        __threadfence();
+        s_ok = ok;
+    }
+    __syncthreads();
+    return s_ok != 0;
+}
+
+struct RunArgs {
+    FitArgs a;                 // the whole batch; part k = samples [k * per, min((k + 1) * per, count))
+    uint64_t per;
+    int n_parts, n_epochs, max_blocks_per_part;
+};
+
+template <int NET, int LOSS, typename T>
+__global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, float* params, double* state,
+                                                              double* __restrict__ partials, double* __restrict__ gsum) {
+    using N = Net<NET>;
+    constexpr int P = N::P;
+    __shared__ __align__(16) float s_w[kSmemW];
+    __shared__ float s_best[ORP_FIT_MAX_PARAMS];
+    __shared__ double s_g[kGsumLen];
+    __shared__ double s_c[16];                     // head of the control block (ST_LR .. ST_COUNT_ACC)
+    __shared__ float s_red[kFitThreads / 32][P + 2];
+    __shared__ float s_lr_t;
+    __shared__ int s_improved;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned int* arrivals = reinterpret_cast<unsigned int*>(state + ST_BARRIER);
+    unsigned int* exits = arrivals + 1;
+    unsigned int* abort_flag = reinterpret_cast<unsigned int*>(state + ST_ABORT);
+
+    load_weights<NET>(s_w, params, tid, kFitThreads);
+    float m = 0.f, v = 0.f;
+    if (tid < P) { m = (float)state[ST_ADAM_M + tid]; v = (float)state[ST_ADAM_V + tid]; s_best[tid] = (float)state[ST_BEST_W + tid]; }
+    if (tid < 16) s_c[tid] = state[tid];
+    __syncthreads();
+    const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
+    const uint32_t G = gridDim.x;
+    unsigned int barriers = 0;
+    bool alive = true;
+
+    for (int e = 0; e < r.n_epochs && alive; ++e) {
+        if (s_c[ST_STOP] != 0.0) break;                                    // same value in every block
+        for (int k = 0; k < r.n_parts && alive; ++k) {
+            // ---- this block's share of batch k
+            FitArgs a = r.a;
+            const uint64_t off = (uint64_t)k * r.per;
+            a.count = min(r.per, r.a.count - off);
+            a.s_t = reinterpret_cast<const char*>(r.a.s_t) + off * sizeof(T);
+            a.s_t1 = reinterpret_cast<const char*>(r.a.s_t1) + off * sizeof(T);
+            a.target = r.a.target + off;
+            if (r.a.feat1) a.feat1 = r.a.feat1 + off;
+            if (r.a.feat2) a.feat2 = r.a.feat2 + off;
+            const uint64_t tile = (uint64_t)kFitThreads * kFitUnroll<NET>;
+            uint64_t want = (a.count + tile - 1) / tile;                  // the grid orp_fit_grad would launch for this batch
+            const uint32_t g_k = (uint32_t)min(want, (uint64_t)min((uint32_t)r.max_blocks_per_part, G));
+            Grads<NET> g;
+            g.zero();
+            float loss = 0.f;
+            uint32_t n = 0;
+            if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, g_k, g, loss, n);
+
+            // ---- block reduction -> partials[parity][k][block]
+            double* part = partials + (size_t)(barriers & 1u) * kGsumLen * G;
+#pragma unroll
+            for (int q = 0; q < P; ++q) {
+                float t = g.get(q);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+                if (lane == 0) s_red[warp][q] = t;
+            }
+            {
+                float l = loss, c = (float)n;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) { l += __shfl_down_sync(0xffffffffu, l, o); c += __shfl_down_sync(0xffffffffu, c, o); }
+                if (lane == 0) { s_red[warp][P] = l; s_red[warp][P + 1] = c; }
+            }
+            __syncthreads();
+            for (int q = tid; q < P + 2; q += kFitThreads) {
+                double t = 0.0;
+                for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[w][q];
+                part[(size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G + blockIdx.x] = t;
+            }
+            // the barrier wait is idle time for everyone but thread 0: the step's learning rate is computed in it
+            if (tid == 32) {
+                double lr = s_c[ST_LR];
+                if (k == 0 && s_c[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)s_c[ST_EPOCH], lr);
+                s_c[ST_LR] = lr;
+                const double t = s_c[ST_ADAM_T] + 1.0;
+                s_c[ST_ADAM_T] = t;
+                s_lr_t = (float)(lr * sqrt(1.0 - pow(0.999, t)) / (1.0 - pow(0.9, t)));
+            }
+            ++barriers;
+            alive = grid_barrier(arrivals, abort_flag, barriers * G);
+            if (!alive) break;
+
+            // ---- every block: fixed-order sum over blocks (same association as fit_reduce_kernel)
+            for (int q0 = warp; q0 < P + 2; q0 += 32) {
+                double t[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int q = q0 + 8 * u;
+                    if (q < P + 2) {
+                        const double* col = part + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G;
+                        for (uint32_t b = lane; b < g_k; b += 32) t[u] += __ldcg(col + b);
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) t[u] += __shfl_down_sync(0xffffffffu, t[u], o);
+                    const int q = q0 + 8 * u;
+                    if (lane == 0 && q < P + 2) s_g[q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)] = t[u];
+                }
+            }
+            __syncthreads();
+
+            // ---- Adam step on the block's own copy (identical in every block)
+            const double inv_n = 1.0 / s_g[ORP_FIT_MAX_PARAMS + 1];
+            if (tid < P) {
+                const float grad = (float)(s_g[tid] * inv_n);
+                float wn = s_w[tid];
+                adam_core(m, v, wn, grad, s_lr_t);
+                s_w[tid] = wn;
+                if (tid >= N::W2 && tid < N::W2 + kH * kH) {
+                    const int q = tid - N::W2;
+                    s_w[kW2T + (q & 7) * kH + (q >> 3)] = wn;
+                }
+            }
+            if (tid == 0) {
+                const double loss_acc = (k == 0 ? 0.0 : s_c[ST_LOSS_ACC]) + s_g[ORP_FIT_MAX_PARAMS];
+                const double cnt_acc = (k == 0 ? 0.0 : s_c[ST_COUNT_ACC]) + s_g[ORP_FIT_MAX_PARAMS + 1];
+                s_c[ST_LOSS_ACC] = loss_acc;
+                s_c[ST_COUNT_ACC] = cnt_acc;
+                s_improved = 0;
+                if (k == r.n_parts - 1) {                                  // epoch end: EarlyStopping bookkeeping (epoch_end())
+                    const double cur = loss_acc / cnt_acc;
+                    s_c[ST_LAST_LOSS] = cur;
+                    int epoch = (int)s_c[ST_EPOCH];
+                    double wait = s_c[ST_WAIT] + 1.0;
+                    if (cur < s_c[ST_BEST]) { s_c[ST_BEST] = cur; wait = 0.0; s_improved = 1; s_c[ST_HAVE_BEST] = 1.0; }
+                    s_c[ST_WAIT] = wait;
+                    if (wait >= s_c[ST_PATIENCE] && epoch > 0) { s_c[ST_STOP] = 1.0; s_c[ST_STOPPED_EARLY] = 1.0; }
+                    epoch += 1;
+                    s_c[ST_EPOCH] = epoch;
+                    s_c[ST_EPOCHS_RUN] = epoch;
+                    s_c[ST_TOTAL_EPOCHS] += 1.0;
+                    if (epoch >= (int)s_c[ST_EPOCHS]) s_c[ST_STOP] = 1.0;
+                }
+            }
+            __syncthreads();
+            if (s_improved && tid < P) s_best[tid] = s_w[tid];             // restore_best_weights=True
+        }
+    }
+
+    // ---- write back (block 0), then the last block out resets the barrier words for the next launch
+    __syncthreads();
+    if (blockIdx.x == 0) {
+        if (tid < P) {
+            params[tid] = s_w[tid];
+            state[ST_ADAM_M + tid] = m;
+            state[ST_ADAM_V + tid] = v;
+            state[ST_BEST_W + tid] = s_best[tid];
+        }
+        if (tid < 16) state[tid] = s_c[tid];
+        for (int q = tid; q < kGsumLen; q += kFitThreads) gsum[q] = s_g[q];
+    }
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        if (atomicAdd(exits, 1u) == G - 1) { *arrivals = 0u; *exits = 0u; }
+    }
 }
 
 // a-10 / a-11: roll-back values at prices@t and the hedge-weight sums.
@@ -713,9 +933,8 @@ __global__ void __launch_bounds__(kMiniThreads, 1) fit_minibatch_kernel(const Fi
             if (tid < N::P) {
                 const float grad = t / (float)nb;
                 const float lr_t = (float)(lr * sqrt(1.0 - pow(0.999, adam_t)) / (1.0 - pow(0.9, adam_t)));
-                m = 0.9f * m + (1.f - 0.9f) * grad;
-                v = 0.999f * v + (1.f - 0.999f) * grad * grad;
-                const float wn = s_w[tid] - lr_t * m / (sqrtf(v) + 1e-7f);
+                float wn = s_w[tid];
+                adam_core(m, v, wn, grad, lr_t);
                 s_w[tid] = wn;
                 if (tid >= N::W2 && tid < N::W2 + kH * kH) {       // keep the transposed copy in step
                     const int k = tid - N::W2;
@@ -767,7 +986,7 @@ extern "C" int orp_fit_n_params(int net) {
     return net == ORP_NET_EO ? Net<ORP_NET_EO>::P : net == ORP_NET_RP ? Net<ORP_NET_RP>::P : -1;
 }
 
-extern "C" uint64_t orp_fit_scratch_bytes(void) { return 512ull * kGsum * sizeof(double); }
+extern "C" uint64_t orp_fit_scratch_bytes(void) { return 2ull * 512ull * kGsum * sizeof(double); }   // two parities (persistent fit)
 
 #define ORP_FIT_DISPATCH(KERNEL_CALL)                                                              \
     do {                                                                                           \
@@ -829,6 +1048,32 @@ extern "C" int orp_fit_epochs(const orp_fit_batch* parts, int n_parts, float* d_
             int rc = fit_step_launch(parts + k, d_params, d_state, d_gsum, d_scratch, flags, (cudaStream_t)stream);
             if (rc) return rc;
         }
+    return ORP_OK;
+}
+
+extern "C" int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
+                           void* d_scratch, int n_epochs, void* stream) {
+    RunArgs r;
+    int rc = make_args(b, r.a, true);
+    if (rc) return rc;
+    ORP_REQUIRE(d_params && d_state && d_gsum && d_scratch, "null pointer");
+    ORP_REQUIRE(n_parts >= 1 && n_epochs >= 0, "n_parts must be >= 1 and n_epochs >= 0");
+    if (n_epochs == 0) return ORP_OK;
+    // the same split as the host layer's: ceil(count / n_parts) samples per batch, the last one possibly shorter
+    uint64_t k = (uint64_t)n_parts < r.a.count ? (uint64_t)n_parts : r.a.count;
+    r.per = (r.a.count + k - 1) / k;
+    r.n_parts = (int)((r.a.count + r.per - 1) / r.per);
+    r.n_epochs = n_epochs;
+    const int unroll = b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>;
+    r.max_blocks_per_part = fit_blocks(r.per, unroll);
+    const int grid = r.max_blocks_per_part;            // <= one block per SM: all blocks are co-resident
+    double* partials = reinterpret_cast<double*>(d_scratch);
+    void* args[] = {(void*)&r, (void*)&d_params, (void*)&d_state, (void*)&partials, (void*)&d_gsum};
+    const void* fn = nullptr;
+#define PICK_RUN(NET, LOSS, T) fn = (const void*)fit_run_kernel<NET, LOSS, T>
+    ORP_FIT_DISPATCH(PICK_RUN);
+#undef PICK_RUN
+    ORP_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kFitThreads), args, 0, (cudaStream_t)stream));
     return ORP_OK;
 }
 

@@ -31,6 +31,9 @@ ST_LR, ST_ADAM_T, ST_EPOCH, ST_EPOCHS, ST_PATIENCE, ST_USE_SCHED, ST_WAIT, ST_BE
 ST_ADAM_M = 16
 ST_ADAM_V = ST_ADAM_M + FIT_MAX_PARAMS
 ST_BEST_W = ST_ADAM_V + FIT_MAX_PARAMS
+ST_TICKET = ST_BEST_W + FIT_MAX_PARAMS
+ST_BARRIER = ST_TICKET + 1
+ST_ABORT = ST_BARRIER + 1
 
 
 class PathParams(C.Structure):
@@ -70,6 +73,7 @@ PROTOTYPES = {
     "orp_fit_update": (C.c_int, [_i32, _vp, _vp, _vp, _i32, _vp]),
     "orp_fit_step": (C.c_int, [C.POINTER(FitBatch), _vp, _vp, _vp, _vp, _i32, _vp]),
     "orp_fit_epochs": (C.c_int, [C.POINTER(FitBatch), _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
+    "orp_fit_run": (C.c_int, [C.POINTER(FitBatch), _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "orp_fit_begin": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
     "orp_fit_init": (C.c_int, [_vp, _vp]),
     "orp_fit_end": (C.c_int, [_i32, _vp, _vp, _vp]),

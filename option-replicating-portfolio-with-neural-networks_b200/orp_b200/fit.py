@@ -51,7 +51,10 @@ class Optimizer:
             _lib.check(_lib.lib().orp_fit_init(_lib.ptr(self.state), _lib.stream_ptr()))
 
     def head(self) -> np.ndarray:
-        return self.state[:16].cpu().numpy()
+        """The 16 scalar control words plus (last entry) the barrier-abort flag, in ONE device-to-host copy."""
+        import torch
+        idx = torch.tensor(list(range(16)) + [_lib.ST_ABORT], device=self.state.device)
+        return self.state[idx].cpu().numpy()
 
 
 class ReplicationNet:
@@ -72,6 +75,7 @@ class ReplicationNet:
         self.sums = torch.zeros(4, dtype=torch.float64, device=self.device)
         self.launches = 0
         self.two_stage = False      # True forces grad -> [all-reduce] -> update even on one GPU (tests, multi-GPU form)
+        self.persistent = True      # False: one launch per optimiser step (orp_fit_epochs) instead of one per fit
 
     def batch(self, s_t, s_t1, target, inv_scale, bond_t, bond_t1, loss="mse", feat1=None, feat2=None):
         torch = _lib.require_cuda()
@@ -126,7 +130,14 @@ class ReplicationNet:
             dist_on = is_distributed(self.group)
             done = 0
             single_launch = mode == "scaled" and not dist_on and not self.two_stage
-            if single_launch:
+            if single_launch and self.persistent:
+                # one process, one GPU: the whole epoch loop is ONE cooperative launch (grid barrier per optimiser step);
+                # the kernel leaves as soon as EarlyStopping fires, so there is nothing to poll
+                _lib.check(L.orp_fit_run(C.byref(batch), int(steps_per_epoch), _lib.ptr(self.params), _lib.ptr(opt.state),
+                                         _lib.ptr(self.gsum), _lib.ptr(self.scratch), int(epochs), st))
+                self.launches += 1
+                done = epochs
+            elif single_launch:
                 parts_arr = (_lib.FitBatch * len(parts))()
                 for k, part in enumerate(parts):
                     C.memmove(C.byref(parts_arr[k]), C.byref(part), C.sizeof(_lib.FitBatch))
@@ -167,6 +178,9 @@ class ReplicationNet:
             _lib.check(L.orp_fit_end(netc, _lib.ptr(self.params), _lib.ptr(opt.state), st))
             self.launches += 2
             h = opt.head()
+            if h[-1] != 0.0:
+                raise RuntimeError("orp_fit_run: a grid barrier timed out (the cooperative grid was not fully resident); "
+                                   "the optimiser state is unusable — create a new Optimizer")
         return {"epochs_run": int(h[_lib.ST_EPOCHS_RUN]), "loss": float(h[_lib.ST_LAST_LOSS]),
                 "stopped_early": bool(h[_lib.ST_STOPPED_EARLY]), "lr": float(h[_lib.ST_LR])}
 

@@ -102,25 +102,27 @@ def test_scaled_fit_tracks_oracle(cuda, net, spe):
 
 @pytest.mark.parametrize("net,n,spe", [("eo", 70_001, 3), ("rp", 5_000, 1), ("eo", 300_000, 8)])
 def test_single_launch_step_equals_two_stage(cuda, net, n, spe):
-    """orp_fit_epochs (grad + fixed-order reduction + update in one launch, epoch loop inside the library) leaves
-    exactly the weights, optimiser state and losses of orp_fit_grad -> orp_fit_update: bit for bit."""
+    """Three drivers of the same fit — orp_fit_run (ONE cooperative launch for all epochs, grid barrier per step),
+    orp_fit_epochs (one launch per optimiser step: the last block reduces and updates) and
+    orp_fit_grad -> orp_fit_update — leave exactly the same weights, optimiser state and losses: bit for bit."""
     from orp_b200.fit import ReplicationNet, Optimizer, init_params
     s_t, s_t1, y, f1, f2 = _toy(n, 4, net)
     bias = 0.1 if net == "eo" else [0.9, 0.1]
     dev = lambda a: torch.from_numpy(a).to(cuda)
     out = []
-    for two_stage in (False, True):
+    for persistent, two_stage in ((True, False), (False, False), (False, True)):
         model = ReplicationNet(net, init_params(net, 1234, bias), cuda)
-        model.two_stage = two_stage
+        model.persistent, model.two_stage = persistent, two_stage
         opt = Optimizer(cuda)
         b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / 100.0, 1.02, 1.03,
                         feat1=dev(f1) if net == "rp" else None, feat2=dev(f2) if net == "rp" else None)
-        h = model.fit(b, opt, epochs=25, patience=4, use_schedule=True, mode="scaled", steps_per_epoch=spe, check_every=7)
-        out.append((h, model.params.cpu().numpy().copy(), opt.state[:400].cpu().numpy().copy(), model.launches))
-    (h0, w0, st0, l0), (h1, w1, st1, l1) = out
-    assert h0 == h1
-    assert np.array_equal(w0, w1) and np.array_equal(st0, st1)
-    assert l0 < l1                      # one launch per optimiser step instead of three
+        hs = [model.fit(b, opt, epochs=25, patience=4, use_schedule=True, mode="scaled", steps_per_epoch=spe, check_every=7),
+              model.fit(b, opt, epochs=9, patience=2, use_schedule=False, mode="scaled", steps_per_epoch=spe, check_every=7)]
+        out.append((hs, model.params.cpu().numpy().copy(), opt.state[:400].cpu().numpy().copy(), model.launches))
+    for hs, w, st, _ in out[1:]:
+        assert hs == out[0][0]
+        assert np.array_equal(w, out[0][1]) and np.array_equal(st, out[0][2])
+    assert out[0][3] < out[1][3] < out[2][3]          # 1 launch per fit < 1 per optimiser step < 3 per optimiser step
 
 
 def test_early_stopping_and_restore(cuda):
