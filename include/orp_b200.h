@@ -209,6 +209,24 @@ int orp_fit_epochs(const orp_fit_batch* parts, int n_parts, float* d_params, dou
 int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
                 void* d_scratch, int n_epochs, void* stream);
 
+/* Multi-GPU form of orp_fit_run (one process per GPU, paths sharded by Sobol index range; no counterpart in the
+ * reference, which is single-process).  The ranks' [gradient, loss, count] vectors are exchanged INSIDE the
+ * persistent kernel: block 0 of every rank stores its vector into every rank's exchange buffer over NVLink and
+ * publishes a step flag; all blocks wait for the flags and add the vectors in rank order, so every GPU applies the
+ * same bits.  Every rank must call with the same n_parts / n_epochs and an equal local sample count.
+ * d_peer_buffers: DEVICE array of `world` pointers, entry r = rank r's buffer as mapped into this process.
+ * Exchange buffers are the one thing this library allocates itself (CUDA IPC needs a cudaMalloc'ed base):
+ *   orp_peer_buffer_create  cudaMalloc + zero + IPC handle (64 bytes) to send to the other ranks
+ *   orp_peer_buffer_open    maps another rank's buffer (cudaIpcOpenMemHandle); orp_peer_buffer_close unmaps it
+ *   orp_peer_buffer_destroy frees this rank's buffer. */
+uint64_t orp_peer_buffer_bytes(void);
+int orp_peer_buffer_create(void** d_buf, unsigned char* handle64);
+int orp_peer_buffer_open(const unsigned char* handle64, void** d_ptr);
+int orp_peer_buffer_close(void* d_ptr);
+int orp_peer_buffer_destroy(void* d_buf);
+int orp_fit_run_peers(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
+                      void* d_scratch, int n_epochs, int rank, int world, void* const* d_peer_buffers, void* stream);
+
 /* Starts a Model.fit call: resets the early-stopping state, keeps weights and Adam moments (they persist across
  * time steps, Replicating_Portfolio.py:203-211).  use_schedule = 1 for the first fit. */
 int orp_fit_begin(double* d_state, int epochs, int patience, int use_schedule, void* stream);

@@ -9,6 +9,8 @@
 // Device-resident control block (`state`, doubles) so that the host can enqueue epochs back to back:
 #include "orp_common.h"
 
+#include <cstring>
+
 namespace orp {
 
 // ---- state layout (indices into the double array) ------------------------------------------------
@@ -634,7 +636,36 @@ struct RunArgs {
     FitArgs a;                 // the whole batch; part k = samples [k * per, min((k + 1) * per, count))
     uint64_t per;
     int n_parts, n_epochs, max_blocks_per_part;
+    int rank, world;           // world = 0: single GPU, no exchange
+    double* const* peers;      // device array of `world` exchange-buffer pointers (peers[rank] = this GPU's own)
 };
+
+// ---- exchange buffer of the multi-GPU fit (one per rank, cudaMalloc'ed, mapped into every peer through CUDA IPC) ----
+// The ranks' [gradient, loss, count] vectors are all-gathered by plain stores over NVLink: block 0 of every rank
+// writes its locally reduced vector into slot [parity][rank] of EVERY rank's buffer, then publishes the step number
+// in flag [parity][rank] with a system-scope release store; every block of every rank waits for all flags of the
+// step (acquire loads from its own memory) and adds the slots in rank order — the same bits on every GPU.  Two
+// parities suffice: a rank can only start step s + 2 after every peer has published step s + 1, i.e. finished reading
+// step s.  No NCCL call, no kernel boundary: the exchange costs one NVLink store latency per optimiser step.
+constexpr int kPeerMaxWorld = 16;
+constexpr int kPeerHdr = 0;                                     // [0] (uint32) steps completed so far
+constexpr int kPeerFlags = 16;                                  // uint32 flags[2][kPeerMaxWorld]
+constexpr int kPeerSlots = 32;                                  // double slots[2][kPeerMaxWorld][kGsumLen]
+constexpr int kPeerDoubles = kPeerSlots + 2 * kPeerMaxWorld * kGsumLen;
+
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ double ld_volatile_f64(const double* p) {
+    double v;
+    asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+    return v;
+}
 
 template <int NET, int LOSS, typename T>
 __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, float* params, double* state,
@@ -662,6 +693,9 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     const uint32_t G = gridDim.x;
     unsigned int barriers = 0;
     bool alive = true;
+    __shared__ int s_peer_ok;
+    double* const xbuf = r.world > 0 ? r.peers[r.rank] : nullptr;                      // this GPU's exchange buffer
+    const unsigned int step0 = r.world > 0 ? *reinterpret_cast<const unsigned int*>(xbuf + kPeerHdr) : 0u;
 
     for (int e = 0; e < r.n_epochs && alive; ++e) {
         if (s_c[ST_STOP] != 0.0) break;                                    // same value in every block
@@ -718,26 +752,67 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             alive = grid_barrier(arrivals, abort_flag, barriers * G);
             if (!alive) break;
 
-            // ---- every block: fixed-order sum over blocks (same association as fit_reduce_kernel)
-            for (int q0 = warp; q0 < P + 2; q0 += 32) {
-                double t[4] = {0.0, 0.0, 0.0, 0.0};
+            // ---- fixed-order sum over this GPU's blocks (same association as fit_reduce_kernel): every block when
+            //      there is one GPU, block 0 alone when the ranks exchange their sums
+            if (r.world == 0 || blockIdx.x == 0) {
+                for (int q0 = warp; q0 < P + 2; q0 += 32) {
+                    double t[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int q = q0 + 8 * u;
-                    if (q < P + 2) {
-                        const double* col = part + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G;
-                        for (uint32_t b = lane; b < g_k; b += 32) t[u] += __ldcg(col + b);
+                    for (int u = 0; u < 4; ++u) {
+                        const int q = q0 + 8 * u;
+                        if (q < P + 2) {
+                            const double* col = part + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G;
+                            for (uint32_t b = lane; b < g_k; b += 32) t[u] += __ldcg(col + b);
+                        }
                     }
-                }
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                    for (int u = 0; u < 4; ++u) {
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) t[u] += __shfl_down_sync(0xffffffffu, t[u], o);
-                    const int q = q0 + 8 * u;
-                    if (lane == 0 && q < P + 2) s_g[q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)] = t[u];
+                        for (int o = 16; o > 0; o >>= 1) t[u] += __shfl_down_sync(0xffffffffu, t[u], o);
+                        const int q = q0 + 8 * u;
+                        if (lane == 0 && q < P + 2) s_g[q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)] = t[u];
+                    }
                 }
             }
             __syncthreads();
+            if (r.world > 0) {
+                const unsigned int step_id = step0 + barriers;                 // the same number on every rank
+                const unsigned int par = step_id & 1u;
+                if (blockIdx.x == 0) {
+                    // push this rank's vector into slot [par][rank] of every rank (plain stores over NVLink) ...
+                    for (int idx = tid; idx < (P + 2) * r.world; idx += kFitThreads) {
+                        const int dst = idx / (P + 2), q = idx - dst * (P + 2);
+                        const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
+                        r.peers[dst][kPeerSlots + ((size_t)par * kPeerMaxWorld + r.rank) * kGsumLen + qq] = s_g[qq];
+                    }
+                    __threadfence_system();
+                    __syncthreads();
+                    // ... then publish the step number
+                    if (tid < r.world)
+                        st_release_sys_u32(reinterpret_cast<unsigned int*>(r.peers[tid] + kPeerFlags) + par * kPeerMaxWorld + r.rank, step_id);
+                }
+                // every block waits until all ranks have published this step (their flags live in OUR memory)
+                if (tid == 0) s_peer_ok = 1;
+                __syncthreads();
+                if (tid < r.world) {
+                    const unsigned int* flag = reinterpret_cast<const unsigned int*>(xbuf + kPeerFlags) + par * kPeerMaxWorld + tid;
+                    unsigned int spins = 0;
+                    while ((int)(ld_acquire_sys_u32(flag) - step_id) < 0) {
+                        if (++spins > (1u << 26) || ld_acquire_u32(abort_flag) != 0u) { atomicExch(abort_flag, 1u); s_peer_ok = 0; break; }
+                    }
+                }
+                __syncthreads();
+                if (!s_peer_ok) { alive = false; break; }
+                // sum the ranks' vectors in rank order: bit-identical on every GPU
+                for (int q = tid; q < P + 2; q += kFitThreads) {
+                    const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
+                    double t = 0.0;
+                    for (int src = 0; src < r.world; ++src)
+                        t += ld_volatile_f64(xbuf + kPeerSlots + ((size_t)par * kPeerMaxWorld + src) * kGsumLen + qq);
+                    s_g[qq] = t;
+                }
+                __syncthreads();
+            }
 
             // ---- Adam step on the block's own copy (identical in every block)
             const double inv_n = 1.0 / s_g[ORP_FIT_MAX_PARAMS + 1];
@@ -788,6 +863,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
         }
         if (tid < 16) state[tid] = s_c[tid];
         for (int q = tid; q < kGsumLen; q += kFitThreads) gsum[q] = s_g[q];
+        if (tid == 0 && r.world > 0) *reinterpret_cast<unsigned int*>(xbuf + kPeerHdr) = step0 + barriers;
     }
     __syncthreads();
     if (tid == 0) {
@@ -1051,8 +1127,8 @@ extern "C" int orp_fit_epochs(const orp_fit_batch* parts, int n_parts, float* d_
     return ORP_OK;
 }
 
-extern "C" int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
-                           void* d_scratch, int n_epochs, void* stream) {
+static int fit_run_launch(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
+                          void* d_scratch, int n_epochs, int rank, int world, double* const* d_peers, cudaStream_t st) {
     RunArgs r;
     int rc = make_args(b, r.a, true);
     if (rc) return rc;
@@ -1064,6 +1140,7 @@ extern "C" int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params,
     r.per = (r.a.count + k - 1) / k;
     r.n_parts = (int)((r.a.count + r.per - 1) / r.per);
     r.n_epochs = n_epochs;
+    r.rank = rank; r.world = world; r.peers = d_peers;
     const int unroll = b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>;
     r.max_blocks_per_part = fit_blocks(r.per, unroll);
     const int grid = r.max_blocks_per_part;            // <= one block per SM: all blocks are co-resident
@@ -1073,7 +1150,56 @@ extern "C" int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params,
 #define PICK_RUN(NET, LOSS, T) fn = (const void*)fit_run_kernel<NET, LOSS, T>
     ORP_FIT_DISPATCH(PICK_RUN);
 #undef PICK_RUN
-    ORP_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kFitThreads), args, 0, (cudaStream_t)stream));
+    ORP_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kFitThreads), args, 0, st));
+    return ORP_OK;
+}
+
+extern "C" int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
+                           void* d_scratch, int n_epochs, void* stream) {
+    return fit_run_launch(b, n_parts, d_params, d_state, d_gsum, d_scratch, n_epochs, 0, 0, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int orp_fit_run_peers(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
+                                 void* d_scratch, int n_epochs, int rank, int world, void* const* d_peer_buffers,
+                                 void* stream) {
+    ORP_REQUIRE(world >= 1 && world <= kPeerMaxWorld, "world must be in [1, %d]", kPeerMaxWorld);
+    ORP_REQUIRE(rank >= 0 && rank < world, "rank must be in [0, world)");
+    ORP_REQUIRE(d_peer_buffers, "null peer table");
+    return fit_run_launch(b, n_parts, d_params, d_state, d_gsum, d_scratch, n_epochs, rank, world,
+                          reinterpret_cast<double* const*>(d_peer_buffers), (cudaStream_t)stream);
+}
+
+extern "C" uint64_t orp_peer_buffer_bytes(void) { return (uint64_t)kPeerDoubles * sizeof(double); }
+
+extern "C" int orp_peer_buffer_create(void** d_buf, unsigned char* handle64) {
+    ORP_REQUIRE(d_buf && handle64, "null pointer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handles are 64 bytes");
+    void* p = nullptr;
+    ORP_CUDA(cudaMalloc(&p, orp_peer_buffer_bytes()));
+    ORP_CUDA(cudaMemset(p, 0, orp_peer_buffer_bytes()));
+    ORP_CUDA(cudaDeviceSynchronize());
+    cudaIpcMemHandle_t h;
+    ORP_CUDA(cudaIpcGetMemHandle(&h, p));
+    memcpy(handle64, &h, 64);
+    *d_buf = p;
+    return ORP_OK;
+}
+
+extern "C" int orp_peer_buffer_open(const unsigned char* handle64, void** d_ptr) {
+    ORP_REQUIRE(handle64 && d_ptr, "null pointer");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    ORP_CUDA(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return ORP_OK;
+}
+
+extern "C" int orp_peer_buffer_close(void* d_ptr) {
+    if (d_ptr) ORP_CUDA(cudaIpcCloseMemHandle(d_ptr));
+    return ORP_OK;
+}
+
+extern "C" int orp_peer_buffer_destroy(void* d_buf) {
+    if (d_buf) ORP_CUDA(cudaFree(d_buf));
     return ORP_OK;
 }
 

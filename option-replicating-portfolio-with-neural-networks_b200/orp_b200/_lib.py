@@ -74,6 +74,12 @@ PROTOTYPES = {
     "orp_fit_step": (C.c_int, [C.POINTER(FitBatch), _vp, _vp, _vp, _vp, _i32, _vp]),
     "orp_fit_epochs": (C.c_int, [C.POINTER(FitBatch), _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
     "orp_fit_run": (C.c_int, [C.POINTER(FitBatch), _i32, _vp, _vp, _vp, _vp, _i32, _vp]),
+    "orp_fit_run_peers": (C.c_int, [C.POINTER(FitBatch), _i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _vp, _vp]),
+    "orp_peer_buffer_bytes": (C.c_uint64, []),
+    "orp_peer_buffer_create": (C.c_int, [C.POINTER(C.c_void_p), _vp]),
+    "orp_peer_buffer_open": (C.c_int, [_vp, C.POINTER(C.c_void_p)]),
+    "orp_peer_buffer_close": (C.c_int, [_vp]),
+    "orp_peer_buffer_destroy": (C.c_int, [_vp]),
     "orp_fit_begin": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
     "orp_fit_init": (C.c_int, [_vp, _vp]),
     "orp_fit_end": (C.c_int, [_i32, _vp, _vp, _vp]),

@@ -18,7 +18,9 @@ import ctypes as C
 import numpy as np
 
 from . import _lib
-from .dist import allreduce_sum_, is_distributed
+import os
+
+from .dist import allreduce_sum_, is_distributed, rank_world
 
 HIDDEN = 8
 NET_IO = {"eo": (1, 1), "rp": (3, 2)}
@@ -41,6 +43,14 @@ def init_params(net: str, seed: int, out_bias) -> np.ndarray:
     return np.concatenate([w1.ravel(), np.zeros(HIDDEN), w2.ravel(), np.zeros(HIDDEN), w3.ravel(), b3]).astype(np.float32)
 
 
+def _nccl_group(group) -> bool:
+    """True when torch.distributed runs over NCCL with more than one rank (one process per GPU on one box)."""
+    if not is_distributed(group):
+        return False
+    import torch.distributed as dist
+    return str(dist.get_backend(group)).lower() == "nccl"
+
+
 class Optimizer:
     """Device-resident Adam + callback state of one compiled Keras model (``keras.optimizers.Adam(1e-3)``)."""
 
@@ -60,7 +70,7 @@ class Optimizer:
 class ReplicationNet:
     """The shared weights of model1/model2 plus scratch buffers; ``fit`` runs one ``Model.fit`` call."""
 
-    def __init__(self, net: str, params0: np.ndarray, device="cuda", group=None):
+    def __init__(self, net: str, params0: np.ndarray, device="cuda", group=None, peer_exchange=None):
         torch = _lib.require_cuda()
         if net not in _lib.NET:
             raise ValueError(f"net must be one of {sorted(_lib.NET)}")
@@ -76,6 +86,70 @@ class ReplicationNet:
         self.launches = 0
         self.two_stage = False      # True forces grad -> [all-reduce] -> update even on one GPU (tests, multi-GPU form)
         self.persistent = True      # False: one launch per optimiser step (orp_fit_epochs) instead of one per fit
+        self.peers = None           # multi-GPU: exchange buffers mapped over CUDA IPC (see _setup_peers)
+        self._equal_counts = {}
+        if peer_exchange is None:
+            peer_exchange = _nccl_group(group) and os.environ.get("ORP_B200_NO_PEERS") is None
+        if peer_exchange:
+            self._setup_peers()
+
+    def _setup_peers(self):
+        """Exchange buffers for the in-kernel all-gather of the [gradient, loss, count] vectors: every rank creates
+        one (the library cudaMallocs it: CUDA IPC needs its own base allocation), the 64-byte IPC handles travel
+        through torch.distributed, and each rank maps the others' buffers.  Single process: a world of one."""
+        torch = _lib.require_cuda()
+        L = _lib.lib()
+        rank, world = rank_world(self.group)
+        with torch.cuda.device(self.device):
+            own = C.c_void_p()
+            handle = (C.c_ubyte * 64)()
+            _lib.check(L.orp_peer_buffer_create(C.byref(own), handle))
+            ptrs, opened = [None] * world, []
+            if world > 1:
+                import torch.distributed as dist
+                handles = [None] * world
+                dist.all_gather_object(handles, bytes(handle), group=self.group)
+                for r, h in enumerate(handles):
+                    if r == rank:
+                        continue
+                    q = C.c_void_p()
+                    buf = (C.c_ubyte * 64).from_buffer_copy(h)
+                    _lib.check(L.orp_peer_buffer_open(buf, C.byref(q)))
+                    ptrs[r] = q.value
+                    opened.append(q.value)
+            ptrs[rank] = own.value
+            table = torch.tensor(ptrs, dtype=torch.int64, device=self.device)
+            if world > 1:
+                import torch.distributed as dist
+                dist.barrier(group=self.group)        # nobody starts exchanging before every mapping exists
+        self.peers = dict(rank=rank, world=world, own=own.value, opened=opened, table=table)
+
+    def close(self):
+        """Unmap the peers' buffers and free this rank's (collective: call on every rank)."""
+        if self.peers is not None:
+            L = _lib.lib()
+            torch = _lib.require_cuda()
+            with torch.cuda.device(self.device):
+                torch.cuda.synchronize()
+                if self.peers["world"] > 1:
+                    import torch.distributed as dist
+                    dist.barrier(group=self.group)    # no rank frees memory a peer's kernel may still write to
+                for q in self.peers["opened"]:
+                    L.orp_peer_buffer_close(q)
+                L.orp_peer_buffer_destroy(self.peers["own"])
+            self.peers = None
+
+    def _ranks_have_equal_counts(self, count: int) -> bool:
+        if count not in self._equal_counts:
+            torch = _lib.require_cuda()
+            if self.peers["world"] == 1:
+                self._equal_counts[count] = True
+            else:
+                import torch.distributed as dist
+                t = torch.tensor([count, -count], dtype=torch.int64, device=self.device)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+                self._equal_counts[count] = int(t[0]) == -int(t[1])
+        return self._equal_counts[count]
 
     def batch(self, s_t, s_t1, target, inv_scale, bond_t, bond_t1, loss="mse", feat1=None, feat2=None):
         torch = _lib.require_cuda()
@@ -130,7 +204,15 @@ class ReplicationNet:
             dist_on = is_distributed(self.group)
             done = 0
             single_launch = mode == "scaled" and not dist_on and not self.two_stage
-            if single_launch and self.persistent:
+            if (mode == "scaled" and self.peers is not None and not self.two_stage
+                    and self._ranks_have_equal_counts(int(batch.count))):
+                # one process per GPU: the same persistent kernel; the ranks' sums are exchanged inside it over NVLink
+                _lib.check(L.orp_fit_run_peers(C.byref(batch), int(steps_per_epoch), _lib.ptr(self.params), _lib.ptr(opt.state),
+                                               _lib.ptr(self.gsum), _lib.ptr(self.scratch), int(epochs),
+                                               self.peers["rank"], self.peers["world"], _lib.ptr(self.peers["table"]), st))
+                self.launches += 1
+                done = epochs
+            elif single_launch and self.persistent:
                 # one process, one GPU: the whole epoch loop is ONE cooperative launch (grid barrier per optimiser step);
                 # the kernel leaves as soon as EarlyStopping fires, so there is nothing to poll
                 _lib.check(L.orp_fit_run(C.byref(batch), int(steps_per_epoch), _lib.ptr(self.params), _lib.ptr(opt.state),
@@ -263,5 +345,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
         v_next, v_cur = v_cur, v_next
         phi0, psi0, v0 = rec["phi"], rec["psi"], rec["mean_V"]
         first = False
-    return {"V0": v0, "phi0": phi0, "psi0": psi0, "steps": steps, "launches": model.launches,
-            "params": model.params[:model.P].cpu().numpy(), "values0": v_next}
+    out = {"V0": v0, "phi0": phi0, "psi0": psi0, "steps": steps, "launches": model.launches,
+           "params": model.params[:model.P].cpu().numpy(), "values0": v_next}
+    model.close()
+    return out

@@ -110,8 +110,9 @@ def test_single_launch_step_equals_two_stage(cuda, net, n, spe):
     bias = 0.1 if net == "eo" else [0.9, 0.1]
     dev = lambda a: torch.from_numpy(a).to(cuda)
     out = []
-    for persistent, two_stage in ((True, False), (False, False), (False, True)):
-        model = ReplicationNet(net, init_params(net, 1234, bias), cuda)
+    for persistent, two_stage, peers in ((True, False, False), (False, False, False), (False, True, False), (True, False, True)):
+        # peers=True: the multi-GPU kernel path (in-kernel exchange of the ranks' sums) with a world of one rank
+        model = ReplicationNet(net, init_params(net, 1234, bias), cuda, peer_exchange=peers)
         model.persistent, model.two_stage = persistent, two_stage
         opt = Optimizer(cuda)
         b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / 100.0, 1.02, 1.03,
@@ -119,6 +120,7 @@ def test_single_launch_step_equals_two_stage(cuda, net, n, spe):
         hs = [model.fit(b, opt, epochs=25, patience=4, use_schedule=True, mode="scaled", steps_per_epoch=spe, check_every=7),
               model.fit(b, opt, epochs=9, patience=2, use_schedule=False, mode="scaled", steps_per_epoch=spe, check_every=7)]
         out.append((hs, model.params.cpu().numpy().copy(), opt.state[:400].cpu().numpy().copy(), model.launches))
+        model.close()
     for hs, w, st, _ in out[1:]:
         assert hs == out[0][0]
         assert np.array_equal(w, out[0][1]) and np.array_equal(st, out[0][2])
