@@ -488,22 +488,30 @@ __device__ __forceinline__ void unpack_raw(const FitArgs& a, const RawSample<NET
 constexpr int kFitS = 2;                                   // samples per thread in flight through the network
 template <int NET> constexpr int kFitUnroll = NET == ORP_NET_EO ? 4 : 2;
 
-// Forward + backward over this block's tiles of one batch: block `block` of `n_blocks` takes tiles block,
-// block + n_blocks, ...  Adds into g / loss / n.
-template <int NET, int LOSS, typename T>
-__device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa, uint32_t block, uint32_t n_blocks,
-                                                 Grads<NET>& g, float& loss, uint32_t& n) {
-    using N = Net<NET>;
-    constexpr int U = kFitUnroll<NET>, S = kFitS;
-    static_assert(U % S == 0, "tile slots are consumed S at a time");
-    const uint64_t tile = (uint64_t)kFitThreads * U, stride = (uint64_t)n_blocks * tile;
-    uint64_t base = (uint64_t)block * tile + threadIdx.x;
-    RawSample<NET, T> cur[U], nxt[U];
+// Issues the loads of this block's FIRST tile of a batch (the persistent kernel does this one optimiser step
+// ahead, so that the latency hides behind the grid barrier and the reduction).
+template <int NET, typename T>
+__device__ __forceinline__ void load_first_tile(const FitArgs& a, uint32_t block, RawSample<NET, T> (&cur)[kFitUnroll<NET>]) {
+    constexpr int U = kFitUnroll<NET>;
+    const uint64_t base = (uint64_t)block * ((uint64_t)kFitThreads * U) + threadIdx.x;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
         cur[u] = RawSample<NET, T>{};
         if (base + (uint64_t)u * kFitThreads < a.count) load_raw<NET, T>(a, base + (uint64_t)u * kFitThreads, cur[u]);
     }
+}
+
+// Forward + backward over this block's tiles of one batch: block `block` of `n_blocks` takes tiles block,
+// block + n_blocks, ...  `cur` holds the first tile (load_first_tile).  Adds into g / loss / n.
+template <int NET, int LOSS, typename T>
+__device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa, uint32_t block, uint32_t n_blocks,
+                                                 RawSample<NET, T> (&cur)[kFitUnroll<NET>], Grads<NET>& g, float& loss, uint32_t& n) {
+    using N = Net<NET>;
+    constexpr int U = kFitUnroll<NET>, S = kFitS;
+    static_assert(U % S == 0, "tile slots are consumed S at a time");
+    const uint64_t tile = (uint64_t)kFitThreads * U, stride = (uint64_t)n_blocks * tile;
+    uint64_t base = (uint64_t)block * tile + threadIdx.x;
+    RawSample<NET, T> nxt[U];
     for (; base < a.count + threadIdx.x; base += stride) {        // block-uniform trip count (base - threadIdx.x < count)
         const uint64_t nb = base + stride;
 #pragma unroll
@@ -552,7 +560,9 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
     g.zero();
     float loss = 0.f;
     uint32_t n = 0;
-    accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, gridDim.x, g, loss, n);
+    RawSample<NET, T> first[kFitUnroll<NET>];
+    load_first_tile<NET, T>(a, blockIdx.x, first);
+    accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, gridDim.x, first, g, loss, n);
     block_reduce_to<NET>(g, loss, n, partials + (size_t)blockIdx.x * kGsum);
     if (STEP) {
         __shared__ bool s_last;
@@ -612,14 +622,19 @@ __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
     return v;
 }
 
-// All threads of all blocks call.  Returns false when the barrier timed out (a block is missing: the launch was
-// not cooperative, or the device is wedged) — every block then leaves the kernel instead of hanging the GPU.
-__device__ __forceinline__ bool grid_barrier(unsigned int* arrivals, unsigned int* abort_flag, unsigned int target) {
-    __shared__ int s_ok;
+// Grid barrier in two halves so that work can sit between "arrive" and "wait".  All threads of all blocks call
+// both.  barrier_wait returns false when the barrier timed out (a block is missing: the launch was not cooperative,
+// or the device is wedged) — every block then leaves the kernel instead of hanging the GPU.
+__device__ __forceinline__ void barrier_arrive(unsigned int* arrivals) {
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
         atomicAdd(arrivals, 1u);
+    }
+}
+__device__ __forceinline__ bool barrier_wait(unsigned int* arrivals, unsigned int* abort_flag, unsigned int target) {
+    __shared__ int s_ok;
+    if (threadIdx.x == 0) {
         int ok = 1;
         unsigned int spins = 0;
         while (ld_acquire_u32(arrivals) < target) {
@@ -632,10 +647,13 @@ __device__ __forceinline__ bool grid_barrier(unsigned int* arrivals, unsigned in
     return s_ok != 0;
 }
 
+struct RunArgs;
+template <typename T> __device__ __forceinline__ FitArgs part_args(const RunArgs& r, int k, uint32_t G, uint32_t& g_k);
+
 struct RunArgs {
     FitArgs a;                 // the whole batch; part k = samples [k * per, min((k + 1) * per, count))
     uint64_t per;
-    int n_parts, n_epochs, max_blocks_per_part;
+    int n_parts, n_epochs, max_blocks_per_part, unroll;
     int rank, world;           // world = 0: single GPU, no exchange
     double* const* peers;      // device array of `world` exchange-buffer pointers (peers[rank] = this GPU's own)
 };
@@ -665,6 +683,23 @@ __device__ __forceinline__ double ld_volatile_f64(const double* p) {
     double v;
     asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
     return v;
+}
+
+// Batch k of the epoch and the number of blocks that work on it (the grid orp_fit_grad would launch for it).
+template <typename T>
+__device__ __forceinline__ FitArgs part_args(const RunArgs& r, int k, uint32_t G, uint32_t& g_k) {
+    FitArgs a = r.a;
+    const uint64_t off = (uint64_t)k * r.per;
+    a.count = min(r.per, r.a.count - off);
+    a.s_t = reinterpret_cast<const char*>(r.a.s_t) + off * sizeof(T);
+    a.s_t1 = reinterpret_cast<const char*>(r.a.s_t1) + off * sizeof(T);
+    a.target = r.a.target + off;
+    if (r.a.feat1) a.feat1 = r.a.feat1 + off;
+    if (r.a.feat2) a.feat2 = r.a.feat2 + off;
+    const uint64_t tile = (uint64_t)kFitThreads * (r.unroll);
+    const uint64_t want = (a.count + tile - 1) / tile;
+    g_k = (uint32_t)min(want, (uint64_t)min((uint32_t)r.max_blocks_per_part, G));
+    return a;
 }
 
 template <int NET, int LOSS, typename T>
@@ -697,26 +732,23 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     double* const xbuf = r.world > 0 ? r.peers[r.rank] : nullptr;                      // this GPU's exchange buffer
     const unsigned int step0 = r.world > 0 ? *reinterpret_cast<const unsigned int*>(xbuf + kPeerHdr) : 0u;
 
+    RawSample<NET, T> first[kFitUnroll<NET>];
+    {
+        uint32_t g0;
+        const FitArgs a0 = part_args<T>(r, 0, G, g0);
+        load_first_tile<NET, T>(a0, blockIdx.x, first);
+    }
     for (int e = 0; e < r.n_epochs && alive; ++e) {
         if (s_c[ST_STOP] != 0.0) break;                                    // same value in every block
         for (int k = 0; k < r.n_parts && alive; ++k) {
-            // ---- this block's share of batch k
-            FitArgs a = r.a;
-            const uint64_t off = (uint64_t)k * r.per;
-            a.count = min(r.per, r.a.count - off);
-            a.s_t = reinterpret_cast<const char*>(r.a.s_t) + off * sizeof(T);
-            a.s_t1 = reinterpret_cast<const char*>(r.a.s_t1) + off * sizeof(T);
-            a.target = r.a.target + off;
-            if (r.a.feat1) a.feat1 = r.a.feat1 + off;
-            if (r.a.feat2) a.feat2 = r.a.feat2 + off;
-            const uint64_t tile = (uint64_t)kFitThreads * kFitUnroll<NET>;
-            uint64_t want = (a.count + tile - 1) / tile;                  // the grid orp_fit_grad would launch for this batch
-            const uint32_t g_k = (uint32_t)min(want, (uint64_t)min((uint32_t)r.max_blocks_per_part, G));
+            // ---- this block's share of batch k (its first tile was requested one step ago)
+            uint32_t g_k;
+            const FitArgs a = part_args<T>(r, k, G, g_k);
             Grads<NET> g;
             g.zero();
             float loss = 0.f;
             uint32_t n = 0;
-            if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, g_k, g, loss, n);
+            if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, g_k, first, g, loss, n);
 
             // ---- block reduction -> partials[parity][k][block]
             double* part = partials + (size_t)(barriers & 1u) * kGsumLen * G;
@@ -739,7 +771,16 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[w][q];
                 part[(size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G + blockIdx.x] = t;
             }
-            // the barrier wait is idle time for everyone but thread 0: the step's learning rate is computed in it
+            // request the first tile of the NEXT optimiser step now: the loads land while the block sits in the barrier
+            // and the reduction (wasted only when the fit stops here)
+            {
+                uint32_t g_next;
+                const FitArgs a_next = part_args<T>(r, k + 1 < r.n_parts ? k + 1 : 0, G, g_next);
+                load_first_tile<NET, T>(a_next, blockIdx.x, first);
+            }
+            ++barriers;
+            barrier_arrive(arrivals);
+            // between arrive and wait: the step's learning rate (two double pow) on a warp that is not the one spinning
             if (tid == 32) {
                 double lr = s_c[ST_LR];
                 if (k == 0 && s_c[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)s_c[ST_EPOCH], lr);
@@ -748,30 +789,34 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 s_c[ST_ADAM_T] = t;
                 s_lr_t = (float)(lr * sqrt(1.0 - pow(0.999, t)) / (1.0 - pow(0.9, t)));
             }
-            ++barriers;
-            alive = grid_barrier(arrivals, abort_flag, barriers * G);
+            alive = barrier_wait(arrivals, abort_flag, barriers * G);
             if (!alive) break;
 
             // ---- fixed-order sum over this GPU's blocks (same association as fit_reduce_kernel): every block when
             //      there is one GPU, block 0 alone when the ranks exchange their sums
             if (r.world == 0 || blockIdx.x == 0) {
-                for (int q0 = warp; q0 < P + 2; q0 += 32) {
-                    double t[4] = {0.0, 0.0, 0.0, 0.0};
+                constexpr int NQ = (P + 2 + 7) / 8;                             // columns per warp: q = warp, warp + 8, ...
+                double t[NQ];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        const int q = q0 + 8 * u;
-                        if (q < P + 2) {
-                            const double* col = part + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G;
-                            for (uint32_t b = lane; b < g_k; b += 32) t[u] += __ldcg(col + b);
+                for (int u = 0; u < NQ; ++u) t[u] = 0.0;
+                for (uint32_t b0 = 0; b0 < g_k; b0 += 128) {                    // 4 x 32 blocks per pass: NQ x 4 loads in flight
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const uint32_t b = b0 + 32 * j + lane;
+#pragma unroll
+                        for (int u = 0; u < NQ; ++u) {
+                            const int q = warp + 8 * u;
+                            if (q < P + 2 && b < g_k)
+                                t[u] += __ldcg(part + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G + b);
                         }
                     }
+                }
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < NQ; ++u) {
 #pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) t[u] += __shfl_down_sync(0xffffffffu, t[u], o);
-                        const int q = q0 + 8 * u;
-                        if (lane == 0 && q < P + 2) s_g[q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)] = t[u];
-                    }
+                    for (int o = 16; o > 0; o >>= 1) t[u] += __shfl_down_sync(0xffffffffu, t[u], o);
+                    const int q = warp + 8 * u;
+                    if (lane == 0 && q < P + 2) s_g[q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)] = t[u];
                 }
             }
             __syncthreads();
@@ -1142,6 +1187,7 @@ static int fit_run_launch(const orp_fit_batch* b, int n_parts, float* d_params, 
     r.n_epochs = n_epochs;
     r.rank = rank; r.world = world; r.peers = d_peers;
     const int unroll = b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>;
+    r.unroll = unroll;
     r.max_blocks_per_part = fit_blocks(r.per, unroll);
     const int grid = r.max_blocks_per_part;            // <= one block per SM: all blocks are co-resident
     double* partials = reinterpret_cast<double*>(d_scratch);
