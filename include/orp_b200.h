@@ -211,9 +211,9 @@ int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params, double* d_
 
 /* Multi-GPU form of orp_fit_run (one process per GPU, paths sharded by Sobol index range; no counterpart in the
  * reference, which is single-process).  The ranks' [gradient, loss, count] vectors are exchanged INSIDE the
- * persistent kernel: block 0 of every rank stores its vector into every rank's exchange buffer over NVLink and
- * publishes a step flag; all blocks wait for the flags and add the vectors in rank order, so every GPU applies the
- * same bits.  Every rank must call with the same n_parts / n_epochs and an equal local sample count.
+ * persistent kernel: block 0 of every rank stores its vector into every rank's exchange buffer over NVLink, the step
+ * number riding inside every 8-byte store; all blocks poll their own GPU's buffer and add the vectors in rank order,
+ * so every GPU applies the same bits.  Every rank must call with the same n_parts / n_epochs and an equal local sample count.
  * d_peer_buffers: DEVICE array of `world` pointers, entry r = rank r's buffer as mapped into this process.
  * Exchange buffers are the one thing this library allocates itself (CUDA IPC needs a cudaMalloc'ed base):
  *   orp_peer_buffer_create  cudaMalloc + zero + IPC handle (64 bytes) to send to the other ranks

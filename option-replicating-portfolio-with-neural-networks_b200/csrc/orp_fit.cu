@@ -659,29 +659,26 @@ struct RunArgs {
 };
 
 // ---- exchange buffer of the multi-GPU fit (one per rank, cudaMalloc'ed, mapped into every peer through CUDA IPC) ----
-// The ranks' [gradient, loss, count] vectors are all-gathered by plain stores over NVLink: block 0 of every rank
-// writes its locally reduced vector into slot [parity][rank] of EVERY rank's buffer, then publishes the step number
-// in flag [parity][rank] with a system-scope release store; every block of every rank waits for all flags of the
-// step (acquire loads from its own memory) and adds the slots in rank order — the same bits on every GPU.  Two
-// parities suffice: a rank can only start step s + 2 after every peer has published step s + 1, i.e. finished reading
-// step s.  No NCCL call, no kernel boundary: the exchange costs one NVLink store latency per optimiser step.
+// The ranks' [gradient, loss, count] vectors are all-gathered by plain stores over NVLink, with the flag travelling
+// INSIDE every 8-byte store (the "LL" idea of collective libraries): a double is sent as two words
+// {low 32 bits, step} and {high 32 bits, step}.  8-byte stores are single-copy atomic, so a receiver that sees
+// the step number it is waiting for in both words has the value — no fence, no separate flag, one NVLink
+// one-way latency.  Block 0 of rank r writes its locally reduced vector into slot [parity][r] of EVERY rank's
+// buffer; every block of every rank polls the `world` slots in its OWN memory and adds them in rank order — the
+// same bits on every GPU.  Two parities suffice: a rank can only send step s + 2 after every peer has sent step
+// s + 1, i.e. after all of that peer's blocks have finished reading step s.
 constexpr int kPeerMaxWorld = 16;
-constexpr int kPeerHdr = 0;                                     // [0] (uint32) steps completed so far
-constexpr int kPeerFlags = 16;                                  // uint32 flags[2][kPeerMaxWorld]
-constexpr int kPeerSlots = 32;                                  // double slots[2][kPeerMaxWorld][kGsumLen]
-constexpr int kPeerDoubles = kPeerSlots + 2 * kPeerMaxWorld * kGsumLen;
+constexpr int kPeerHdr = 0;                                     // word 0 (uint32): optimiser steps completed so far
+constexpr int kPeerSlots = 32;                                  // uint2 slots[2][kPeerMaxWorld][2 * kGsumLen], in 8-byte words
+constexpr int kPeerSlotWords = 2 * kGsumLen;
+constexpr int kPeerDoubles = kPeerSlots + 2 * kPeerMaxWorld * kPeerSlotWords;
 
-__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int* p) {
-    unsigned int v;
-    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
+__device__ __forceinline__ void st_ll(double* word, unsigned int data, unsigned int flag) {
+    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(word), "r"(data), "r"(flag) : "memory");
 }
-__device__ __forceinline__ void st_release_sys_u32(unsigned int* p, unsigned int v) {
-    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ double ld_volatile_f64(const double* p) {
-    double v;
-    asm volatile("ld.volatile.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+__device__ __forceinline__ uint2 ld_ll(const double* word) {
+    uint2 v;
+    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(word) : "memory");
     return v;
 }
 
@@ -821,42 +818,45 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             }
             __syncthreads();
             if (r.world > 0) {
-                const unsigned int step_id = step0 + barriers;                 // the same number on every rank
+                const unsigned int step_id = step0 + barriers;                 // the same number on every rank, never 0
                 const unsigned int par = step_id & 1u;
                 if (blockIdx.x == 0) {
-                    // push this rank's vector into slot [par][rank] of every rank (plain stores over NVLink) ...
+                    // send: {low half, step} and {high half, step} of every entry into slot [par][rank] of every rank
                     for (int idx = tid; idx < (P + 2) * r.world; idx += kFitThreads) {
                         const int dst = idx / (P + 2), q = idx - dst * (P + 2);
                         const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
-                        r.peers[dst][kPeerSlots + ((size_t)par * kPeerMaxWorld + r.rank) * kGsumLen + qq] = s_g[qq];
+                        const double val = s_g[qq];
+                        double* w = r.peers[dst] + kPeerSlots + ((size_t)par * kPeerMaxWorld + r.rank) * kPeerSlotWords + 2 * qq;
+                        st_ll(w, (unsigned int)__double2loint(val), step_id);
+                        st_ll(w + 1, (unsigned int)__double2hiint(val), step_id);
                     }
-                    __threadfence_system();
-                    __syncthreads();
-                    // ... then publish the step number
-                    if (tid < r.world)
-                        st_release_sys_u32(reinterpret_cast<unsigned int*>(r.peers[tid] + kPeerFlags) + par * kPeerMaxWorld + r.rank, step_id);
                 }
-                // every block waits until all ranks have published this step (their flags live in OUR memory)
+                // receive (every block, from its own GPU's memory): poll until both words of an entry carry this step,
+                // then add the ranks' values in rank order: bit-identical on every GPU
                 if (tid == 0) s_peer_ok = 1;
                 __syncthreads();
-                if (tid < r.world) {
-                    const unsigned int* flag = reinterpret_cast<const unsigned int*>(xbuf + kPeerFlags) + par * kPeerMaxWorld + tid;
-                    unsigned int spins = 0;
-                    while ((int)(ld_acquire_sys_u32(flag) - step_id) < 0) {
-                        if (++spins > (1u << 26) || ld_acquire_u32(abort_flag) != 0u) { atomicExch(abort_flag, 1u); s_peer_ok = 0; break; }
-                    }
-                }
-                __syncthreads();
-                if (!s_peer_ok) { alive = false; break; }
-                // sum the ranks' vectors in rank order: bit-identical on every GPU
                 for (int q = tid; q < P + 2; q += kFitThreads) {
                     const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
                     double t = 0.0;
-                    for (int src = 0; src < r.world; ++src)
-                        t += ld_volatile_f64(xbuf + kPeerSlots + ((size_t)par * kPeerMaxWorld + src) * kGsumLen + qq);
+                    for (int src = 0; src < r.world; ++src) {
+                        const double* w = xbuf + kPeerSlots + ((size_t)par * kPeerMaxWorld + src) * kPeerSlotWords + 2 * qq;
+                        uint2 lo = ld_ll(w), hi = ld_ll(w + 1);
+                        unsigned int spins = 0;
+                        while (lo.y != step_id || hi.y != step_id) {
+                            if (++spins > (1u << 24) || (((spins & 1023u) == 0u) && ld_acquire_u32(abort_flag) != 0u)) {
+                                atomicExch(abort_flag, 1u);
+                                s_peer_ok = 0;
+                                break;
+                            }
+                            lo = ld_ll(w);
+                            hi = ld_ll(w + 1);
+                        }
+                        t += __hiloint2double((int)hi.x, (int)lo.x);
+                    }
                     s_g[qq] = t;
                 }
                 __syncthreads();
+                if (!s_peer_ok) { alive = false; break; }
             }
 
             // ---- Adam step on the block's own copy (identical in every block)
