@@ -432,28 +432,75 @@ __device__ __forceinline__ void reduce_partials(const double* __restrict__ parti
 constexpr int kFitThreads = 256;
 constexpr int kGsum = kGsumLen;
 
-template <int NET>
-__device__ __forceinline__ void block_reduce_to(const Grads<NET>& g, float loss, uint32_t n, double* __restrict__ dst) {
-    constexpr int P = Net<NET>::P;
-    __shared__ float s_red[kFitThreads / 32][P + 2];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// Sum over the 32 lanes of a warp of N per-lane values, as a reduce-scatter: at every stage a lane keeps one half
+// of its values and hands the other half to its partner, so N values cost about N shuffles instead of 5 N.
+// Afterwards lane l holds, in a[0 .. N/32), the warp totals of the entries i + (N/32) * bit-weighted(l) — see
+// scattered_index().  N must be a multiple of 32; the association is fixed, hence deterministic.
+template <int N>
+__device__ __forceinline__ void warp_reduce_scatter(float (&a)[N], int lane) {
+    static_assert(N % 32 == 0, "pad to a multiple of the warp size");
+    int len = N;
 #pragma unroll
-    for (int k = 0; k < P; ++k) {
-        float v = g.get(k);
+    for (int off = 16; off > 0; off >>= 1) {
+        const int half = len / 2;
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < N / 2; ++i) {
+            if (i < half) {
+                const float lo = a[i], hi = a[i + half];
+                const float send = up ? lo : hi, keep = up ? hi : lo;
+                a[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+        }
+        len = half;
+    }
+}
+template <int N>
+__device__ __forceinline__ int scattered_index(int i, int lane) {
+    constexpr int R = N / 32;
+    return i + R * ((lane & 1) + 2 * ((lane >> 1) & 1) + 4 * ((lane >> 2) & 1) + 8 * ((lane >> 3) & 1) + 16 * ((lane >> 4) & 1));
+}
+
+// Block total of the per-thread gradients, loss and sample count as ONE fp64 vector: warp reduce-scatter ->
+// shared memory -> sum over the 8 warps in warp order -> dst[index * stride] (index = k for the gradient of
+// parameter k, ORP_FIT_MAX_PARAMS for the loss, + 1 for the count).  Shared by every driver of the fit.
+template <int NET>
+__device__ __forceinline__ void block_partial(const Grads<NET>& g, float loss, uint32_t n, float (&s_red)[kFitThreads / 32][Net<NET>::P + 2],
+                                              double* __restrict__ dst, size_t stride) {
+    constexpr int P = Net<NET>::P;
+    constexpr int N = P + 2;
+    constexpr int NB = (N % 32) <= 4 ? (N / 32) * 32 : ((N + 31) / 32) * 32;      // EO: 96 (+ 3 by the classic tree); RP: 128
+    constexpr int REST = N > NB ? N - NB : 0;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float a[NB];
+#pragma unroll
+    for (int k = 0; k < NB; ++k) a[k] = k < P ? g.get(k) : (k == P ? loss : (k == P + 1 ? (float)n : 0.f));
+    warp_reduce_scatter<NB>(a, lane);
+#pragma unroll
+    for (int i = 0; i < NB / 32; ++i) {
+        const int q = scattered_index<NB>(i, lane);
+        if (q < N) s_red[warp][q] = a[i];
+    }
+#pragma unroll
+    for (int k = NB; k < NB + REST; ++k) {
+        float v = k < P ? g.get(k) : (k == P ? loss : (float)n);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
         if (lane == 0) s_red[warp][k] = v;
     }
-    float l = loss, c = (float)n;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) { l += __shfl_down_sync(0xffffffffu, l, o); c += __shfl_down_sync(0xffffffffu, c, o); }
-    if (lane == 0) { s_red[warp][P] = l; s_red[warp][P + 1] = c; }
     __syncthreads();
-    for (int k = threadIdx.x; k < P + 2; k += kFitThreads) {
+    for (int q = threadIdx.x; q < N; q += kFitThreads) {
         double t = 0.0;
-        for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[w][k];
-        dst[k < P ? k : ORP_FIT_MAX_PARAMS + (k - P)] = t;
+#pragma unroll
+        for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[w][q];
+        dst[(size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * stride] = t;
     }
+}
+
+template <int NET>
+__device__ __forceinline__ void block_reduce_to(const Grads<NET>& g, float loss, uint32_t n, double* __restrict__ dst) {
+    __shared__ float s_red[kFitThreads / 32][Net<NET>::P + 2];
+    block_partial<NET>(g, loss, n, s_red, dst, 1);
 }
 
 // Raw inputs of one sample, as loaded (conversion to the network's fp32 happens when the sample is used).
@@ -647,6 +694,22 @@ __device__ __forceinline__ bool barrier_wait(unsigned int* arrivals, unsigned in
     return s_ok != 0;
 }
 
+// Optional phase timestamps (build with -DORP_FIT_TRACE; tools/trace_fit.py): blocks 0 and G-1 write %globaltimer at
+// eight points of each of the first 512 optimiser steps into the unused tail of the scratch buffer.
+#ifdef ORP_FIT_TRACE
+#define ORP_TRACE(phase)                                                                                          \
+    do {                                                                                                          \
+        if (threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && barriers_done_for_trace < 512) { \
+            unsigned long long t_;                                                                                \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                \
+            reinterpret_cast<unsigned long long*>(partials)[(600 * 1024) / 8 +                                     \
+                ((blockIdx.x == 0 ? 0 : 512) + barriers_done_for_trace) * 8 + (phase)] = t_;                     \
+        }                                                                                                         \
+    } while (0)
+#else
+#define ORP_TRACE(phase) do { } while (0)
+#endif
+
 struct RunArgs;
 template <typename T> __device__ __forceinline__ FitArgs part_args(const RunArgs& r, int k, uint32_t G, uint32_t& g_k);
 
@@ -711,6 +774,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     __shared__ float s_red[kFitThreads / 32][P + 2];
     __shared__ float s_lr_t;
     __shared__ int s_improved;
+    __shared__ double s_num[kFitThreads], s_den[kFitThreads];      // Adam bias terms of the next 256 steps
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned int* arrivals = reinterpret_cast<unsigned int*>(state + ST_BARRIER);
     unsigned int* exits = arrivals + 1;
@@ -739,6 +803,10 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
         if (s_c[ST_STOP] != 0.0) break;                                    // same value in every block
         for (int k = 0; k < r.n_parts && alive; ++k) {
             // ---- this block's share of batch k (its first tile was requested one step ago)
+#ifdef ORP_FIT_TRACE
+            const unsigned int barriers_done_for_trace = barriers;
+#endif
+            ORP_TRACE(0);
             uint32_t g_k;
             const FitArgs a = part_args<T>(r, k, G, g_k);
             Grads<NET> g;
@@ -746,28 +814,11 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             float loss = 0.f;
             uint32_t n = 0;
             if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, g_k, first, g, loss, n);
+            ORP_TRACE(1);
 
             // ---- block reduction -> partials[parity][k][block]
             double* part = partials + (size_t)(barriers & 1u) * kGsumLen * G;
-#pragma unroll
-            for (int q = 0; q < P; ++q) {
-                float t = g.get(q);
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
-                if (lane == 0) s_red[warp][q] = t;
-            }
-            {
-                float l = loss, c = (float)n;
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) { l += __shfl_down_sync(0xffffffffu, l, o); c += __shfl_down_sync(0xffffffffu, c, o); }
-                if (lane == 0) { s_red[warp][P] = l; s_red[warp][P + 1] = c; }
-            }
-            __syncthreads();
-            for (int q = tid; q < P + 2; q += kFitThreads) {
-                double t = 0.0;
-                for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[w][q];
-                part[(size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G + blockIdx.x] = t;
-            }
+            block_partial<NET>(g, loss, n, s_red, part + blockIdx.x, G);
             // request the first tile of the NEXT optimiser step now: the loads land while the block sits in the barrier
             // and the reduction (wasted only when the fit stops here)
             {
@@ -775,37 +826,55 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 const FitArgs a_next = part_args<T>(r, k + 1 < r.n_parts ? k + 1 : 0, G, g_next);
                 load_first_tile<NET, T>(a_next, blockIdx.x, first);
             }
+            ORP_TRACE(2);
             ++barriers;
             barrier_arrive(arrivals);
-            // between arrive and wait: the step's learning rate (two double pow) on a warp that is not the one spinning
+            ORP_TRACE(3);
+            // between arrive and wait: the step's learning rate.  Its two double pow() per step come from a table that
+            // all threads refill together every 256 steps (thread i: step t + i), so they stay off the critical path.
+            if (((barriers - 1u) & (kFitThreads - 1u)) == 0u) {
+                const double ti = s_c[ST_ADAM_T] + 1.0 + (double)tid;
+                s_num[tid] = sqrt(1.0 - pow(0.999, ti));
+                s_den[tid] = 1.0 - pow(0.9, ti);
+                __syncthreads();
+            }
             if (tid == 32) {
                 double lr = s_c[ST_LR];
                 if (k == 0 && s_c[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)s_c[ST_EPOCH], lr);
                 s_c[ST_LR] = lr;
-                const double t = s_c[ST_ADAM_T] + 1.0;
-                s_c[ST_ADAM_T] = t;
-                s_lr_t = (float)(lr * sqrt(1.0 - pow(0.999, t)) / (1.0 - pow(0.9, t)));
+                s_c[ST_ADAM_T] = s_c[ST_ADAM_T] + 1.0;
+                const unsigned int i = (barriers - 1u) & (kFitThreads - 1u);
+                s_lr_t = (float)(lr * s_num[i] / s_den[i]);
             }
             alive = barrier_wait(arrivals, abort_flag, barriers * G);
+            ORP_TRACE(4);
             if (!alive) break;
 
             // ---- fixed-order sum over this GPU's blocks (same association as fit_reduce_kernel): every block when
             //      there is one GPU, block 0 alone when the ranks exchange their sums
             if (r.world == 0 || blockIdx.x == 0) {
                 constexpr int NQ = (P + 2 + 7) / 8;                             // columns per warp: q = warp, warp + 8, ...
+                constexpr int NJ = 5;                                           // 5 x 32 blocks per pass
                 double t[NQ];
 #pragma unroll
                 for (int u = 0; u < NQ; ++u) t[u] = 0.0;
-                for (uint32_t b0 = 0; b0 < g_k; b0 += 128) {                    // 4 x 32 blocks per pass: NQ x 4 loads in flight
+                for (uint32_t b0 = 0; b0 < g_k; b0 += 32 * NJ) {
+                    // all NQ x NJ loads are issued before the first add: one L2 round trip, not one per group
+                    double v[NJ][NQ];
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const uint32_t b = b0 + 32 * j + lane;
+                    for (int j = 0; j < NJ; ++j) {
+                        const uint32_t b = min(b0 + 32 * j + lane, g_k - 1);    // clamped: out-of-range lanes re-read a valid entry
 #pragma unroll
                         for (int u = 0; u < NQ; ++u) {
-                            const int q = warp + 8 * u;
-                            if (q < P + 2 && b < g_k)
-                                t[u] += __ldcg(part + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G + b);
+                            const int q = min(warp + 8 * u, P + 1);
+                            v[j][u] = __ldcg(part + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G + b);
                         }
+                    }
+#pragma unroll
+                    for (int j = 0; j < NJ; ++j) {
+                        const bool in = b0 + 32 * j + lane < g_k;
+#pragma unroll
+                        for (int u = 0; u < NQ; ++u) t[u] += in ? v[j][u] : 0.0;      // same order as fit_reduce_kernel: b ascending
                     }
                 }
 #pragma unroll
@@ -817,6 +886,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 }
             }
             __syncthreads();
+            ORP_TRACE(5);
             if (r.world > 0) {
                 const unsigned int step_id = step0 + barriers;                 // the same number on every rank, never 0
                 const unsigned int par = step_id & 1u;
@@ -859,6 +929,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 if (!s_peer_ok) { alive = false; break; }
             }
 
+            ORP_TRACE(6);
             // ---- Adam step on the block's own copy (identical in every block)
             const double inv_n = 1.0 / s_g[ORP_FIT_MAX_PARAMS + 1];
             if (tid < P) {
@@ -894,6 +965,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             }
             __syncthreads();
             if (s_improved && tid < P) s_best[tid] = s_w[tid];             // restore_best_weights=True
+            ORP_TRACE(7);
         }
     }
 

@@ -11,7 +11,7 @@ import sys
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _PKG = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_PKG, "liborp_b200.so")
+LIB_PATH = os.environ.get("ORP_B200_LIB") or os.path.join(_PKG, "liborp_b200.so")      # override: instrumented builds
 
 ORP_OK, ORP_E_VALUE, ORP_E_CUDA, ORP_E_STATE = 0, -1, -2, -3
 MODEL = {"gbm_log": 0, "gbm_arith": 1, "gbm_euler": 1, "sv": 2, "linear": 3}
