@@ -247,6 +247,24 @@ int orp_fit_predict(const orp_fit_batch* b, const float* d_params, float* d_valu
 int orp_fit_epoch_minibatch(const orp_fit_batch* b, float* d_params, double* d_state, int batch_size,
                             uint64_t epoch_seed, void* stream);
 
+/* ---------------------------------------------------------------- §8f-1  per-step risk metrics (device) */
+
+/* d_resid_out[i] = target_i - (phi_i * S_{t+1} + psi_i * B_{t+1}) in network units: the array the reference calls VaR
+ * (get_phi_psi_VaR, Replicating_Portfolio.py:120), computed with the weights as they stand after the step's fits. */
+int orp_fit_residuals(const orp_fit_batch* b, const float* d_params, float* d_resid_out, void* stream);
+
+/* Radix select for np.quantile(VaR, q) (Replicating_Portfolio.py:122) without sorting or host copies of the array.
+ * orp_select_hist ADDS to d_hist[ORP_SELECT_BINS] (caller zeroes it) the histogram of the 8-bit digit at `shift` of the
+ * order-preserving key, over the elements whose key agrees with `prefix` on the bits of `mask`; bin 256 counts NaNs.
+ * Four passes (shift 24, 16, 8, 0) pin the k-th smallest element; the caller picks the digit between passes (after
+ * summing the ranks' histograms on several GPUs).  key -> float: key & 0x80000000 ? key ^ 0x80000000 : ~key.
+ * orp_select_next: d_out[0] += #{key <= `key`}, d_out[1] = min(d_out[1], smallest key above `key`) — the successor
+ * needed for numpy's linear interpolation (caller initialises d_out = {0, 0xffffffff}). */
+#define ORP_SELECT_BINS 257
+int orp_select_hist(const float* d_x, uint64_t n, int shift, uint32_t prefix, uint32_t mask,
+                    unsigned long long* d_hist, void* stream);
+int orp_select_next(const float* d_x, uint64_t n, uint32_t key, unsigned long long* d_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

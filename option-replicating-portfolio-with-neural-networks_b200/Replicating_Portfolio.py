@@ -12,6 +12,7 @@ What runs where (reference lines in brackets):
   ``liborp_b200.so``;
 * survivors ``N_t`` [:78-84]: NumPy's legacy ``RandomState.binomial`` on the host, re-seeded per step as in
   the reference — a sequential variable-rejection stream that only NumPy can reproduce bit for bit;
+* the per-step ``VaR`` quantiles [:120-122]: radix select on the device (``orp_b200.quantiles``);
 * plots, DataFrames, per-path Python lists [:117-123, 229-231]: not reproduced; the means they end in are
   reduced on the device.
 
@@ -103,10 +104,15 @@ def _run(params, model, sim_params):
         print(f'\n>> Y_({(t_i + 1) * dt_red:.2f}) = {float(Y_tm[t_i + 1].mean()):.3f}, '
               f'N_({(t_i + 1) * dt_red:.2f}) = {float(N_NN[t_i + 1].mean()):.3f}')
 
+    def risk(rec):                                                 # the reference's per-step print [:122]
+        print(f'VaR: {rec["VaR"][0]:4f} (98%),  {rec["VaR"][1]:4f} (99%)')
+
+    chatty = params.get('verbose', True)
     res = fit_replication(Y_tm, B, terminal, net='rp', mode=params.get('mode', 'scaled'), scale=1.0,
                           out_bias=[1 - out_of_money_P, out_of_money_P], init_seed=params.get('init_seed', 1234),
                           features=features, second_model=True, cost_of_capital=COST_OF_CAPITAL,
-                          verbose=False, on_step=progress if params.get('verbose', True) else None)
+                          verbose=False, on_step=progress if chatty else None,
+                          var_quantiles=(.98, .99) if chatty else None, on_step_end=risk if chatty else None)
     phi = np.float64(res['phi0'] * ADJUSTMENT_FACTOR)
     psi = np.float64(res['psi0'] * ADJUSTMENT_FACTOR)
     return phi, psi

@@ -1041,6 +1041,24 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitAr
     }
 }
 
+// §8f-1: the per-path replication residual ("VaR" of get_phi_psi_VaR): y - V(prices at t+1), current weights.
+template <int NET, typename T>
+__global__ void __launch_bounds__(kFitThreads, 4) fit_residual_kernel(const FitArgs a, const float* __restrict__ params,
+                                                                     float* __restrict__ resid) {
+    using N = Net<NET>;
+    __shared__ __align__(16) float s_w[kSmemW];
+    load_weights<NET>(s_w, params, threadIdx.x, kFitThreads);
+    __syncthreads();
+    const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
+    for (uint64_t i = (uint64_t)blockIdx.x * kFitThreads + threadIdx.x; i < a.count; i += (uint64_t)gridDim.x * kFitThreads) {
+        float x[1][N::IN], s_t, s_t1[1], phi[1], psi[1], v1[1];
+        Acts<NET, 1> act;
+        load_sample<NET, T>(a, i, x[0], s_t, s_t1[0]);
+        net_forward<NET, 1>(s_wa, x, s_t1, a.b_t1, act, phi, psi, v1);          // features at t, prices at t+1 (X1)
+        resid[i] = a.target[i] - v1[0];
+    }
+}
+
 __global__ void predict_reduce_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ sums) {
     if (threadIdx.x >= 4) return;
     double t = 0.0;
@@ -1376,6 +1394,27 @@ extern "C" int orp_fit_predict(const orp_fit_batch* b, const float* d_params, fl
     ORP_LAUNCH_CHECK("fit_predict_kernel");
     predict_reduce_kernel<<<1, 32, 0, st>>>(partials, grid, d_sums);
     ORP_LAUNCH_CHECK("predict_reduce_kernel");
+    return ORP_OK;
+}
+
+extern "C" int orp_fit_residuals(const orp_fit_batch* b, const float* d_params, float* d_resid_out, void* stream) {
+    FitArgs a;
+    int rc = make_args(b, a, true);
+    if (rc) return rc;
+    ORP_REQUIRE(d_params && d_resid_out, "null pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    uint64_t want = (a.count + kFitThreads - 1) / kFitThreads;
+    const uint64_t cap = (uint64_t)(4 * sm_count() < 512 ? 4 * sm_count() : 512);
+    const int grid = (int)(want < cap ? want : cap);
+    const bool f64 = b->paths_dtype == ORP_F64;
+    if (b->net == ORP_NET_EO) {
+        if (f64) fit_residual_kernel<ORP_NET_EO, double><<<grid, kFitThreads, 0, st>>>(a, d_params, d_resid_out);
+        else     fit_residual_kernel<ORP_NET_EO, float><<<grid, kFitThreads, 0, st>>>(a, d_params, d_resid_out);
+    } else {
+        if (f64) fit_residual_kernel<ORP_NET_RP, double><<<grid, kFitThreads, 0, st>>>(a, d_params, d_resid_out);
+        else     fit_residual_kernel<ORP_NET_RP, float><<<grid, kFitThreads, 0, st>>>(a, d_params, d_resid_out);
+    }
+    ORP_LAUNCH_CHECK("fit_residual_kernel");
     return ORP_OK;
 }
 

@@ -266,6 +266,15 @@ class ReplicationNet:
         return {"epochs_run": int(h[_lib.ST_EPOCHS_RUN]), "loss": float(h[_lib.ST_LAST_LOSS]),
                 "stopped_early": bool(h[_lib.ST_STOPPED_EARLY]), "lr": float(h[_lib.ST_LR])}
 
+    def residuals(self, batch, out):
+        """``out[i] = target_i - V(X1)_i`` with the current weights: the reference's per-path ``VaR`` array
+        (``get_phi_psi_VaR``, ``Replicating_Portfolio.py:120``), kept on the device."""
+        torch = _lib.require_cuda()
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().orp_fit_residuals(C.byref(batch), _lib.ptr(self.params), _lib.ptr(out), _lib.stream_ptr()))
+            self.launches += 1
+        return out
+
     def predict(self, batch, values_out=None):
         """``model.predict(X0)`` into ``values_out`` (fp32) and the global sums
         ``(sum V, sum phi, sum psi, sum |y - V(X1)|)`` as a 4-vector on the host."""
@@ -283,7 +292,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
                     epochs_first: int = 500, epochs_next: int = 100, patience_first: int = 50, patience_next: int = 7,
                     batch_size: int = 512, shuffle_seed: int = 0, features=None, second_model: bool = False,
                     cost_of_capital: float = 0.1, check_every: int = 16, verbose: bool = False, on_step=None,
-                    steps_per_epoch: int = 8):
+                    steps_per_epoch: int = 8, var_quantiles=None, on_step_end=None):
     """Backward replication over all kept columns.
 
     ``paths_tm``: TIME-MAJOR ``(n_cols, count)`` CUDA tensor of this rank's paths; ``bond``: ``n_cols`` bond
@@ -294,6 +303,10 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
     notebook's own ratio (4096 paths / batch 512, ``European Options.ipynb`` cell 13), kept at every scale.  ``second_model=True`` adds the
     pinball-loss fit of the SAME weights and the blend ``values = g + cost_of_capital (h - g)``
     (``Replicating_Portfolio.py:217-221``; the reference's model2 aliases model1's layers).
+
+    ``var_quantiles`` (e.g. ``(.98, .99)``): per step, the quantiles of the replication residual
+    ``values[:, t+1] - phi Y_{t+1} - psi B_{t+1}`` over ALL paths of all ranks (``Replicating_Portfolio.py:120-122``),
+    by radix select on the device; reported as ``steps[i]["VaR"]``.  ``on_step_end(rec)`` is called with each record.
 
     Returns ``dict(V0, phi0, psi0, steps=[...], launches)`` in network units."""
     torch = _lib.require_cuda()
@@ -315,6 +328,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
     v_cur = torch.empty_like(v_next)
     h_buf = torch.empty_like(v_next) if second_model else None
     steps, first = [], True
+    resid_buf = None
     phi0 = psi0 = v0 = float("nan")
     for t_i in range(n_cols - 2, -1, -1):
         if on_step is not None:
@@ -339,7 +353,15 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
             # get_phi_psi_VaR reads the shared 'Phi_Psi' layer after BOTH fits (Replicating_Portfolio.py:104-115)
             rec.update(epochs_run2=h2["epochs_run"], loss2=h2["loss"], phi=sums2[1] / total, psi=sums2[2] / total,
                        mean_V=sums[0] / total + cost_of_capital * (sums2[0] - sums[0]) / total)
+        if var_quantiles is not None:
+            from .risk import quantiles
+            if resid_buf is None:
+                resid_buf = torch.empty_like(v_next)
+            model.residuals(b2 if second_model else b, resid_buf)          # weights as they stand after the step's fits
+            rec["VaR"] = quantiles(resid_buf, var_quantiles, group).tolist()
         steps.append(rec)
+        if on_step_end is not None:
+            on_step_end(rec)
         if verbose:
             print(rec)
         v_next, v_cur = v_cur, v_next

@@ -47,6 +47,7 @@ def test_replicating_portfolio_dropin_notebook_call(cuda, capsys):
     phi, psi = RP.Replicating_Portfolio(dict(PARAMETERS))
     out = capsys.readouterr().out
     assert "reduction = 25" in out and ">> Y_(" in out                        # the reference's prints (RP.py:92, :194)
+    assert out.count("VaR: ") == 40 and "(98%)" in out and "(99%)" in out       # one per rebalancing step (RP.py:122)
     _check(phi, psi, 634_349, 350_176)
 
 

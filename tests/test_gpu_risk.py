@@ -1,0 +1,84 @@
+"""GPU tests of the per-step risk metrics: device quantiles by radix select against
+``np.quantile`` — the call the reference makes on its per-path ``VaR`` array (``Replicating_Portfolio.py:122``).
+
+Order statistics are selected exactly (integer keys), the interpolation is NumPy's ``_lerp`` in fp64: results must
+agree to 1e-12 relative with ``np.quantile`` of the same fp32 values promoted to fp64."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+QS = [0.0, 0.02, 0.5, 0.98, 0.985, 0.99, 0.995, 1.0]
+
+
+def _check(x, qs=QS):
+    import orp_b200
+    got = orp_b200.quantiles(torch.from_numpy(x).cuda(), qs)
+    ref = np.quantile(x.astype(np.float64), qs)
+    np.testing.assert_allclose(got, ref, rtol=1e-12, atol=0)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 257, 4099, 1_000_003])
+def test_quantiles_match_numpy(cuda, n):
+    rng = np.random.default_rng(n)
+    _check((rng.standard_normal(n) * 3).astype(np.float32))
+
+
+def test_quantiles_ties_signs_and_infinities(cuda):
+    rng = np.random.default_rng(5)
+    x = np.concatenate([np.zeros(500), -np.zeros(500), np.full(300, 1.5), rng.integers(-3, 4, 5000).astype(np.float64),
+                        [1e-45, -1e-45, 3e38, -3e38]]).astype(np.float32)
+    rng.shuffle(x)
+    _check(x)
+    # infinities: NumPy's own lerp turns (b - a) * g into NaN next to an infinity; the device path mirrors it
+    y = np.concatenate([x, [np.inf, np.inf, -np.inf]]).astype(np.float32)
+    qs = [0.0, 1e-5, 0.5, 0.99999, 1.0]
+    got = __import__("orp_b200").quantiles(torch.from_numpy(y).cuda(), qs)
+    with np.errstate(invalid="ignore"):
+        ref = np.quantile(y.astype(np.float64), qs)
+    np.testing.assert_array_equal(got, ref)
+
+
+def test_quantiles_nan_and_errors(cuda):
+    import orp_b200
+    x = torch.tensor([1.0, float("nan"), 3.0], device=cuda)
+    assert np.isnan(orp_b200.quantiles(x, [0.5, 0.99])).all()            # like np.quantile
+    with pytest.raises(ValueError, match="range"):
+        orp_b200.quantiles(torch.ones(4, device=cuda), [1.5])
+    with pytest.raises(ValueError):
+        orp_b200.quantiles(torch.ones(4, device=cuda, dtype=torch.float64), [0.5])
+
+
+def test_step_var_quantiles_are_the_quantiles_of_the_residuals(cuda):
+    """fit_replication(var_quantiles=...) reports, per time step, np.quantile of  values[:, t+1] - V(X1)  (the
+    reference's VaR array) with the weights left by that step's fits."""
+    import orp_b200
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 4)
+    tm = orp_b200.simulate_paths("gbm_log", p, m=13, steps=4, device=cuda, time_major=True)
+    vals = torch.empty(2 ** 13, dtype=torch.float32, device=cuda)
+    orp_b200.payoff_sums(tm, [100.0], [-1], "call", values_out=vals, value_scale=0.01)
+    res = orp_b200.fit_replication(tm, orp_b200.bond_curve(0.05, 1.0, 5), vals, net="eo", scale=100.0,
+                                   epochs_first=30, epochs_next=5, var_quantiles=(.98, .99))
+    assert all(len(st["VaR"]) == 2 and st["VaR"][0] <= st["VaR"][1] for st in res["steps"])
+    # last step (t_i = 0): recompute the residuals with the returned weights
+    model = ReplicationNet("eo", res["params"], cuda)
+    # values[:, 1] is not returned; check the terminal step instead by refitting nothing: residuals of a fresh model
+    b = model.batch(tm[3], tm[4], vals, 1 / 100.0, float(orp_b200.bond_curve(0.05, 1.0, 5)[3]),
+                    float(orp_b200.bond_curve(0.05, 1.0, 5)[4]))
+    r = model.residuals(b, torch.empty_like(vals))
+    got = orp_b200.quantiles(r, (.98, .99))
+    np.testing.assert_allclose(got, np.quantile(r.cpu().numpy().astype(np.float64), (.98, .99)), rtol=1e-12)
+    # and against the network evaluated by the oracle on the host
+    from oracle import fit as ofit
+    S = tm.t().cpu().numpy()
+    bond = orp_b200.bond_curve(0.05, 1.0, 5)
+    st = torch.from_numpy((S[:, 3] / 100).astype(np.float32))
+    st1 = torch.from_numpy((S[:, 4] / 100).astype(np.float32))
+    p1 = torch.stack([st1, torch.full_like(st, np.float32(bond[4] / 100))], dim=1)
+    v1, _, _ = ofit.forward(torch.from_numpy(res["params"].copy()), "eo", st[:, None], p1)
+    ref = vals.cpu().numpy() - v1.numpy()
+    np.testing.assert_allclose(r.cpu().numpy(), ref, atol=2e-6)
