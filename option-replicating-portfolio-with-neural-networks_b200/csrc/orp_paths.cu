@@ -102,14 +102,35 @@ __device__ __forceinline__ void store_col(void* out, uint64_t ld, int col, uint6
 // models whose state is the level itself (no exp at the kept columns)
 template <int MODEL> constexpr bool kLevel = MODEL == ORP_MODEL_GBM_ARITH || MODEL == ORP_MODEL_LINEAR;
 
+// exp(x) for the one-step log-increments of the multiplicative form (MULT): degree-9 Taylor series inside
+// |x| < 1/8 (remainder x^10 / 10! < 3e-16 relative), the library exp outside — including -inf, +inf and NaN,
+// which fail the comparison.  The host only selects MULT when six standard deviations stay inside the fast range.
+__device__ __forceinline__ double exp_step(double x) {
+    if (fabs(x) < 0.125) {
+        double p = 1.0 / 362880.0;
+        p = fma(p, x, 1.0 / 40320.0);
+        p = fma(p, x, 1.0 / 5040.0);
+        p = fma(p, x, 1.0 / 720.0);
+        p = fma(p, x, 1.0 / 120.0);
+        p = fma(p, x, 1.0 / 24.0);
+        p = fma(p, x, 1.0 / 6.0);
+        p = fma(p, x, 0.5);
+        p = fma(p, x, 1.0);
+        return fma(p, x, 1.0);
+    }
+    return exp(x);
+}
+
 // One time step for the two paths of a lane.  z: normals of the price engine, y: of the volatility engine.
-template <int MODEL>
+// MULT (log-models only): the state is the price itself and is multiplied by exp_step(increment), so that storing
+// a column costs nothing; otherwise the state is the log-price and exp() is taken at the kept columns.
+template <int MODEL, bool MULT = false>
 __device__ __forceinline__ void advance(const PathArgs& a, double& s_0, double& s_1, double& v_0, double& v_1,
                                         double z0, double z1, double y0, double y1) {
     if (MODEL == ORP_MODEL_GBM_LOG) {
         // lnS_t = lnS_{t-1} + ((r - sigma^2/2) dt + sigma sqrt(dt) W_t)                      EO cell 6
-        s_0 += fma(a.c_vol, z0, a.c_drift);
-        s_1 += fma(a.c_vol, z1, a.c_drift);
+        if (MULT) { s_0 *= exp_step(fma(a.c_vol, z0, a.c_drift)); s_1 *= exp_step(fma(a.c_vol, z1, a.c_drift)); }
+        else { s_0 += fma(a.c_vol, z0, a.c_drift); s_1 += fma(a.c_vol, z1, a.c_drift); }
     } else if (MODEL == ORP_MODEL_GBM_ARITH) {
         // Y_t = Y_{t-1} + Y_{t-1} (mu dt + sigma sqrt(dt) W_t)                                RP.py:65
         s_0 = fma(s_0, fma(a.c_vol, z0, a.c_drift), s_0);
@@ -122,8 +143,9 @@ __device__ __forceinline__ void advance(const PathArgs& a, double& s_0, double& 
         // v_t = v + a (b - v) + c sqrt(v dt) Wv_t;  lnY_t = lnY + ((mu - v_t^2/2) dt + v_t sqrt(dt) W_t)   RP.py:285-287
         v_0 = (v_0 + a.a * (a.b - v_0)) + (a.c * sqrt(v_0 * a.dt)) * y0;
         v_1 = (v_1 + a.a * (a.b - v_1)) + (a.c * sqrt(v_1 * a.dt)) * y1;
-        s_0 += (a.c_drift - 0.5 * (v_0 * v_0)) * a.dt + (v_0 * a.c_vol) * z0;
-        s_1 += (a.c_drift - 0.5 * (v_1 * v_1)) * a.dt + (v_1 * a.c_vol) * z1;
+        const double i0 = (a.c_drift - 0.5 * (v_0 * v_0)) * a.dt + (v_0 * a.c_vol) * z0;
+        const double i1 = (a.c_drift - 0.5 * (v_1 * v_1)) * a.dt + (v_1 * a.c_vol) * z1;
+        if (MULT) { s_0 *= exp_step(i0); s_1 *= exp_step(i1); } else { s_0 += i0; s_1 += i1; }
     }
 }
 
@@ -141,8 +163,10 @@ __host__ __device__ inline size_t tlane_smem_bytes(int n_steps) { return (size_t
 // TLS: the lane tables (256 B per dimension and engine) are staged in shared memory behind the coefficient table
 // when they fit (D <= ~300 for two engines); otherwise they are read through L1.
 // ALL: keep_every == 1, every step is stored (no keep test in the loop).
-template <int MODEL, typename OutT, bool FUSED, bool TLS, bool ALL>
+// MULT: log-models with every column stored and small steps — price state, exp_step() per step, no exp() per column.
+template <int MODEL, typename OutT, bool FUSED, bool TLS, bool ALL, bool MULT>
 __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a) {
+    static_assert(!MULT || (ALL && !FUSED && !kLevel<MODEL>), "MULT is the keep-every-1 form of the unfused log-models");
     static_assert(!FUSED || MODEL == ORP_MODEL_GBM_LOG, "only the log-Euler GBM step fuses into the table");
     extern __shared__ __align__(128) char s_tab[];
     load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
@@ -181,7 +205,7 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
 
         // state: GBM_LOG ln S; GBM_ARITH S; SV ln Y and v
         double s_0, s_1, v_0 = a.v0, v_1 = a.v0;
-        if (kLevel<MODEL> || FUSED) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
+        if (kLevel<MODEL> || FUSED || MULT) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
         OutT* __restrict__ optr = reinterpret_cast<OutT*>(a.out) + j0;       // running column pointer (+32 = second path)
         if (ok0) optr[0] = (OutT)a.s0;
         if (ok1) optr[32] = (OutT)a.s0;
@@ -222,11 +246,11 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
                         y0 = ndtri_bits(base_b ^ tb.x, tab);
                         y1 = ndtri_bits(base_b ^ tb.y, tab);
                     }
-                    advance<MODEL>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
+                    advance<MODEL, MULT>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
                 }
                 if (ALL || t == next_keep) {
                     double o0 = s_0, o1 = s_1;
-                    if (!kLevel<MODEL> && !FUSED) { o0 = exp(s_0); o1 = exp(s_1); }
+                    if (!kLevel<MODEL> && !FUSED && !MULT) { o0 = exp(s_0); o1 = exp(s_1); }
                     optr += a.ld;
                     if (ok0) optr[0] = (OutT)o0;
                     if (ok1) optr[32] = (OutT)o1;
@@ -248,7 +272,7 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
 struct BridgeOp { int32_t dim; int32_t emits; double wl, wr, sd; };
 constexpr int kBridgeMaxDepth = 20;
 
-template <int MODEL, typename OutT>
+template <int MODEL, typename OutT, bool MULT>
 __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const PathArgs a, const BridgeOp* __restrict__ ops) {
     extern __shared__ __align__(128) char s_tab[];
     load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
@@ -270,7 +294,7 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
         const uint64_t j0 = i0 - a.start, j1 = i1 - a.start;
 
         double s_0, s_1, v_0 = a.v0, v_1 = a.v0;
-        if (kLevel<MODEL>) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
+        if (kLevel<MODEL> || MULT) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
         if (ok0) store_col<OutT>(a.out, a.ld, 0, j0, a.s0);
         if (ok1) store_col<OutT>(a.out, a.ld, 0, j1, a.s0);
         int next_keep = a.keep_every, col = 1, t = 0, sp = -1;
@@ -315,10 +339,10 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
                     for (int q = 0; q < NS; ++q) { const double wj = stk[q][sp]; inc[q] = wj - cur[q]; cur[q] = wj; }
                     --sp;
                     ++t;
-                    advance<MODEL>(a, s_0, s_1, v_0, v_1, inc[0], inc[1], inc[NS - 2], inc[NS - 1]);
+                    advance<MODEL, MULT>(a, s_0, s_1, v_0, v_1, inc[0], inc[1], inc[NS - 2], inc[NS - 1]);
                     if (t == next_keep) {
                         double q0 = s_0, q1 = s_1;
-                        if (!kLevel<MODEL>) { q0 = exp(s_0); q1 = exp(s_1); }
+                        if (!kLevel<MODEL> && !MULT) { q0 = exp(s_0); q1 = exp(s_1); }
                         if (ok0) store_col<OutT>(a.out, a.ld, col, j0, q0);
                         if (ok1) store_col<OutT>(a.out, a.ld, col, j1, q1);
                         next_keep += a.keep_every;
@@ -338,14 +362,21 @@ static int set_table_smem(K kernel, size_t bytes = kNdtriTableBytes) {
 
 constexpr size_t kMaxDynSmem = 227 * 1024;       // per-block opt-in limit on sm_100
 
-template <int MODEL, typename OutT, bool FUSED, bool TLS, bool ALL>
+// Six standard deviations of a one-step log-increment stay inside exp_step()'s series range (|x| < 1/8)?
+static bool small_steps(const PathArgs& a, int model) {
+    if (model == ORP_MODEL_GBM_LOG) return 6.0 * fabs(a.c_vol) + fabs(a.c_drift) < 0.125;
+    const double v = fmax(fabs(a.v0), fabs(a.b)) * 1.5;            // SV: a bound on the volatility level (beyond it exp_step falls back to exp)
+    return 6.0 * v * fabs(a.c_vol) + fabs(a.c_drift - 0.5 * v * v) * fabs(a.dt) < 0.125;
+}
+
+template <int MODEL, typename OutT, bool FUSED, bool TLS, bool ALL, bool MULT = false>
 static int launch_paths_v(const PathArgs& a, size_t smem, cudaStream_t st) {
-    int rc = set_table_smem(paths_kernel<MODEL, OutT, FUSED, TLS, ALL>, smem);
+    int rc = set_table_smem(paths_kernel<MODEL, OutT, FUSED, TLS, ALL, MULT>, smem);
     if (rc) return rc;
     const uint64_t n_tiles = (a.start + a.count - 1) / kWarpPaths - a.start / kWarpPaths + 1;
     const uint64_t want = (n_tiles + 31) / 32;
     const int grid = (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
-    paths_kernel<MODEL, OutT, FUSED, TLS, ALL><<<grid, kPathThreads, smem, st>>>(a);
+    paths_kernel<MODEL, OutT, FUSED, TLS, ALL, MULT><<<grid, kPathThreads, smem, st>>>(a);
     ORP_LAUNCH_CHECK("paths_kernel");
     return ORP_OK;
 }
@@ -356,6 +387,11 @@ static int launch_paths(const PathArgs& a, cudaStream_t st) {
     const size_t with_tl = kNdtriTableBytes + engines * tlane_smem_bytes(a.n_steps);
     const bool tls = with_tl <= kMaxDynSmem && !getenv("ORP_B200_NO_TLS");
     const bool all = a.keep_every == 1;
+    if constexpr (!FUSED && (MODEL == ORP_MODEL_GBM_LOG || MODEL == ORP_MODEL_SV)) {
+        if (all && small_steps(a, MODEL) && !getenv("ORP_B200_NO_MULT"))
+            return tls ? launch_paths_v<MODEL, OutT, false, true, true, true>(a, with_tl, st)
+                       : launch_paths_v<MODEL, OutT, false, false, true, true>(a, kNdtriTableBytes, st);
+    }
     if (tls) return all ? launch_paths_v<MODEL, OutT, FUSED, true, true>(a, with_tl, st)
                         : launch_paths_v<MODEL, OutT, FUSED, true, false>(a, with_tl, st);
     return all ? launch_paths_v<MODEL, OutT, FUSED, false, true>(a, kNdtriTableBytes, st)
@@ -363,16 +399,25 @@ static int launch_paths(const PathArgs& a, cudaStream_t st) {
 }
 
 
-template <int MODEL, typename OutT>
-static int launch_paths_bridge(const PathArgs& a, const void* d_bridge, cudaStream_t st) {
-    int rc = set_table_smem(paths_bridge_kernel<MODEL, OutT>);
+template <int MODEL, typename OutT, bool MULT>
+static int launch_paths_bridge_v(const PathArgs& a, const void* d_bridge, cudaStream_t st) {
+    int rc = set_table_smem(paths_bridge_kernel<MODEL, OutT, MULT>);
     if (rc) return rc;
     const uint64_t n_tiles = (a.start + a.count - 1) / kWarpPaths - a.start / kWarpPaths + 1;
     const uint64_t want = (n_tiles + 31) / 32;
     const int grid = (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
-    paths_bridge_kernel<MODEL, OutT><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a, reinterpret_cast<const BridgeOp*>(d_bridge));
+    paths_bridge_kernel<MODEL, OutT, MULT><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a, reinterpret_cast<const BridgeOp*>(d_bridge));
     ORP_LAUNCH_CHECK("paths_bridge_kernel");
     return ORP_OK;
+}
+
+template <int MODEL, typename OutT>
+static int launch_paths_bridge(const PathArgs& a, const void* d_bridge, cudaStream_t st) {
+    if constexpr (MODEL == ORP_MODEL_GBM_LOG || MODEL == ORP_MODEL_SV) {
+        if (a.keep_every <= 2 && small_steps(a, MODEL) && !getenv("ORP_B200_NO_MULT"))
+            return launch_paths_bridge_v<MODEL, OutT, true>(a, d_bridge, st);
+    }
+    return launch_paths_bridge_v<MODEL, OutT, false>(a, d_bridge, st);
 }
 
 }  // namespace orp
