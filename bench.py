@@ -112,6 +112,23 @@ class Pipeline:
         self.vals = torch.empty(self.count, dtype=torch.float32, device=device)
         self.bond = orp_b200.bond_curve(CFG["r"], CFG["T"], D + 1)
         self.ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        # C4-style sweep on the same path set: 8 strikes x 8 maturity columns = 64 European calls in one payoff call
+        self.sweep_k = np.repeat(np.linspace(80.0, 120.0, 8), 8)
+        self.sweep_c = np.tile(np.minimum(np.arange(1, 9) * (D // 8) + D % 8, D), 8)
+
+    def sweep(self, reps=5):
+        """Options priced per second (north_star's second throughput figure): 64 (strike, maturity) pairs sharing this
+        rank's stored paths; device time of the payoff-and-reduction kernels, all-reduce of the 128 sums included."""
+        torch, orp = self.torch, self.orp
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        orp.price_european(self.paths, self.sweep_k, self.sweep_c, "call", r=CFG["r"], dt=CFG["T"] / self.D, total_paths=2 ** self.m)
+        e0.record()
+        for _ in range(reps):
+            prices, _ = orp.price_european(self.paths, self.sweep_k, self.sweep_c, "call", r=CFG["r"], dt=CFG["T"] / self.D,
+                                           total_paths=2 ** self.m)
+        e1.record()
+        torch.cuda.synchronize()
+        return 64 * reps / (e0.elapsed_time(e1) * 1e-3), prices
 
     def step(self, fresh_engine=False):
         torch, orp = self.torch, self.orp
@@ -196,6 +213,16 @@ def run_reference(args):
     return 0
 
 
+def sweep_err(prices, pipe):
+    from math import erf, exp, log, sqrt
+    def bs(K, T):
+        N = lambda x: 0.5 * (1.0 + erf(x / sqrt(2.0)))
+        d1 = (log(CFG["S0"] / K) + (CFG["r"] + 0.5 * CFG["sigma"] ** 2) * T) / (CFG["sigma"] * sqrt(T))
+        return CFG["S0"] * N(d1) - K * exp(-CFG["r"] * T) * N(d1 - CFG["sigma"] * sqrt(T))
+    ref = np.array([bs(k, c * CFG["T"] / pipe.D) for k, c in zip(pipe.sweep_k, pipe.sweep_c)])
+    return float(np.abs(np.asarray(prices) - ref).max())
+
+
 def workload_name(m, D):
     return (f"C5: 2^{m} Sobol paths x {D} steps log-Euler GBM fp64 (S0=K=100,T=1,r=.05,sigma=.2), all columns stored, "
             f"call payoff, full backward replication ({D} fits, EO net, scaled mode)")
@@ -248,10 +275,11 @@ def run_own(args):
     ev[3].record()
     barrier()
     e2e_elapsed = ev[2].elapsed_time(ev[3]) * 1e-3 / n_e2e
-    tt = torch.tensor([elapsed, e2e_elapsed], dtype=torch.float64, device=device)
+    opts_per_s, sweep_prices = pipe.sweep()
+    tt = torch.tensor([elapsed, e2e_elapsed, 1.0 / opts_per_s], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    elapsed, e2e_elapsed = (float(x) for x in tt.cpu())
+    elapsed, e2e_elapsed, inv_opts = (float(x) for x in tt.cpu())
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -289,6 +317,9 @@ def run_own(args):
         "path_stage_path_steps_per_s": total_steps / world / (t_paths * 1e-3) * world,
         "e2e": {"value": total_steps / e2e_elapsed, "unit": "path-steps/s", "h2d_bytes_per_step": int(eng.sv32.nbytes + eng.tlane.nbytes),
                 "d2h_bytes_per_step": int(16 + 16 * 8 * (D + 2) + 32 * D)},
+        "options_priced_per_s": {"value": 1.0 / inv_opts, "what": "64 European calls (8 strikes x 8 maturities) off the stored path set of this "
+                                 "workload, payoff_partial + payoff_final kernels + all-reduce (C4-shaped sweep)",
+                                 "max_abs_err_vs_black_scholes": sweep_err(sweep_prices, pipe)},
         "gpu_launches": int(sum(s["launches"] for s in stages)),
         "clocks": clocks,
         "result": {"V0_nn": last["V0"], "phi0": last["phi0"], "psi0": last["psi0"], "price_mc": last["price_mc"], "p_otm": last["p_otm"]},

@@ -158,13 +158,21 @@ def payoff_sums(paths_tm, strikes, columns, kind: str = "call", s0: float = 0.0,
     if not paths_tm.is_contiguous():
         raise ValueError("paths_tm must be the contiguous time-major tensor")
     dt = _lib.F64 if paths_tm.dtype == torch.float64 else _lib.F32
+    # The kernel handles options in chunks of 8 and reads a maturity column once per chunk it appears in: group the
+    # options by column (option 0 stays first: it owns values_out) so a 64-option sweep over 8 maturities streams 8
+    # columns instead of 64.  Results are returned in the caller's order.
+    order = np.concatenate([[0], 1 + np.argsort(columns[1:], kind="stable")]).astype(np.int64)
+    strikes_s, columns_s = np.ascontiguousarray(strikes[order]), np.ascontiguousarray(columns[order])
     with torch.cuda.device(paths_tm.device):
         sums = torch.empty(n_opt, dtype=torch.float64, device=paths_tm.device)
         otm = torch.empty(n_opt, dtype=torch.float64, device=paths_tm.device)
         _lib.check(_lib.lib().orp_payoff_reduce(
-            _lib.ptr(paths_tm), dt, count, count, _lib.PAYOFF[kind], n_opt, _lib.ptr(strikes), _lib.ptr(columns),
+            _lib.ptr(paths_tm), dt, count, count, _lib.PAYOFF[kind], n_opt, _lib.ptr(strikes_s), _lib.ptr(columns_s),
             float(s0), float(value_scale), _lib.ptr(values_out), _lib.ptr(sums), _lib.ptr(otm),
             _lib.ptr(_payoff_scratch(paths_tm.device, n_opt)), _lib.stream_ptr()))
+        if n_opt > 1 and not np.array_equal(order, np.arange(n_opt)):
+            inv = torch.from_numpy(np.argsort(order)).to(paths_tm.device)
+            sums, otm = sums[inv], otm[inv]
     return sums, otm
 
 

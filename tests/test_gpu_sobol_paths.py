@@ -228,3 +228,22 @@ def test_large_run_properties(cuda):
     # an oracle window in the middle of the big run
     ref = opaths.simulate_window("gbm_log", p, D + 1, 3_000_000, 256)
     np.testing.assert_allclose(tm[:, 3_000_000:3_000_256].t().cpu().numpy(), ref, rtol=RTOL64)
+
+
+def test_c4_strike_maturity_sweep_64_options(cuda):
+    """BASELINE config C4 in small: 64 European calls (8 strikes x 8 maturity columns) priced off ONE 252-step GBM
+    Sobol set in one payoff call; sums against the oracle (1e-9), prices against Black-Scholes (Euler + QMC error)."""
+    import orp_b200
+    p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 252)
+    m, D = 14, 252
+    strikes = np.repeat(np.linspace(80.0, 120.0, 8), 8)
+    cols = np.tile(np.arange(1, 9) * 31 + 4, 8)                     # 35, 66, ..., 252
+    tm = orp_b200.simulate_paths("gbm_log", p, m=m, steps=D, device=cuda, time_major=True)
+    sums, otm = orp_b200.payoff_sums(tm, strikes, cols, "call")
+    rs, ro = opaths.payoff_sums_window("gbm_log", p, D + 1, 0, 2 ** m, strikes, cols, "call")
+    np.testing.assert_allclose(sums.cpu().numpy(), rs, rtol=1e-9)
+    assert np.array_equal(otm.cpu().numpy(), ro)
+    prices, p_otm = orp_b200.price_european(tm, strikes, cols, "call", r=0.05, dt=1 / 252)
+    bs = np.array([opaths.black_scholes_call(100.0, k, c / 252, 0.05, 0.2) for k, c in zip(strikes, cols)])
+    assert np.abs(prices - bs).max() < 0.1              # QMC error of 2^14 paths in the far out-of-the-money corner
+    assert ((p_otm >= 0) & (p_otm <= 1)).all()
