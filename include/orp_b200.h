@@ -265,6 +265,17 @@ int orp_select_hist(const float* d_x, uint64_t n, int shift, uint32_t prefix, ui
                     unsigned long long* d_hist, void* stream);
 int orp_select_next(const float* d_x, uint64_t n, uint32_t key, unsigned long long* d_out, void* stream);
 
+/* ---------------------------------------------------------------- §8f-2  survivors (device) */
+
+/* Replaces the binomial thinning loop of Replicating_Portfolio.py:78-84 for path counts the host loop cannot reach:
+ * N_t ~ Binomial(N_{t-1}, exp(-lambda_t dt)) per path, lambda time-major as written by orp_paths (ORP_MODEL_LINEAR),
+ * d_lambda[t * ld + j], t = 0..n_steps.  The reference's NumPy legacy stream is sequential and irreproducible in
+ * parallel; the draws here come from Philox4x32-10 keyed by `seed` and indexed by (start + j, t), so they do not
+ * depend on the sharding.  Parity with the reference is distributional.  d_out[col * ld_out + j] = N_t / n0 (fp32)
+ * at t = col * keep_every, col = 0 .. n_steps / keep_every. */
+int orp_survivors(const void* d_lambda, int dtype, uint64_t ld, uint64_t start, uint64_t count, int n_steps,
+                  int keep_every, double n0, double dt, uint64_t seed, float* d_out, uint64_t ld_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

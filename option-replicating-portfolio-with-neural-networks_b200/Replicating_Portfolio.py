@@ -10,14 +10,15 @@ What runs where (reference lines in brackets):
 * fund paths ``Y`` [:60-65 / :274-289], mortality intensity ``lambda`` [:72-76], payoff and summary
   statistics [:87-89], the per-step MLP fits, roll-back and hedge-weight means [:193-235]: CUDA kernels of
   ``liborp_b200.so``;
-* survivors ``N_t`` [:78-84]: NumPy's legacy ``RandomState.binomial`` on the host, re-seeded per step as in
-  the reference — a sequential variable-rejection stream that only NumPy can reproduce bit for bit;
+* survivors ``N_t`` [:78-84]: up to 2^16 paths NumPy's legacy ``RandomState.binomial`` on the host, re-seeded per
+  step as in the reference — a sequential variable-rejection stream that only NumPy can reproduce bit for bit;
+  beyond that (or with ``survivors='device'``) the same binomial thinning from a counter-based generator on the GPU;
 * the per-step ``VaR`` quantiles [:120-122]: radix select on the device (``orp_b200.quantiles``);
 * plots, DataFrames, per-path Python lists [:117-123, 229-231]: not reproduced; the means they end in are
   reduced on the device.
 
 Imports neither TensorFlow nor matplotlib.  Optional keys beyond the reference's: ``mode`` (``'scaled'``
-default, ``'keras'`` = serial batch-512 mini-batches), ``init_seed``, ``device``, ``verbose``.
+default, ``'keras'`` = serial batch-512 mini-batches), ``init_seed``, ``device``, ``verbose``, ``survivors``.
 Like the reference, importing the module seeds NumPy's global generator with 1234 [:27].
 """
 from __future__ import annotations
@@ -47,13 +48,23 @@ def _simulate_common(params, model, sim_params, n_time_steps, reduction, device)
     return kept, terminal
 
 
-def _mortality(params, n_time_steps, dt, device):
-    """``L_paths`` on the device (seed 1234, ``:72-76``) and ``N_paths`` on the host (``:78-84``)."""
+def _mortality(params, n_time_steps, dt, reduction, device):
+    """``L_paths`` on the device (seed 1234, ``:72-76``) and ``N_paths / N`` at the kept columns (``:78-84, 93``).
+
+    ``params['survivors']``: ``'host'`` — NumPy's legacy ``RandomState.binomial`` re-seeded per step exactly as the
+    reference does (bit-identical ``N_paths``, but a host loop over a ``(steps, paths)`` array); ``'device'`` — the
+    same binomial thinning drawn from a counter-based generator on the GPU (distributional parity, any path count);
+    default: host up to 2^16 paths, device beyond."""
     import torch
-    from orp_b200 import simulate_paths
+    from orp_b200 import simulate_paths, survivors
     m = params['n_paths']
     L_tm = simulate_paths('linear', {'S0': params['l0'], 'mu': params['c'], 'sigma': params['ita'], 'dt': dt},
                           m=m, steps=n_time_steps - 1, seed=1234, device=device, time_major=True)
+    where = params.get('survivors', 'host' if m <= 16 else 'device')
+    if where == 'device':
+        return L_tm, survivors(L_tm, params['N'], dt, keep_every=reduction, seed=1234).to(torch.float64)
+    if where != 'host':
+        raise ValueError("params['survivors'] must be 'host' or 'device'")
     L_host = L_tm.cpu().numpy()                                   # (n_time_steps, paths)
     N_paths = np.empty((n_time_steps, 2 ** m), dtype=int)
     N_paths[0] = params['N']
@@ -61,7 +72,7 @@ def _mortality(params, n_time_steps, dt, device):
         probabilities = np.exp(-L_host[t] * dt)
         np.random.seed(1234 + t)                                  # as the reference: reproducible draws
         N_paths[t] = np.random.binomial(N_paths[t - 1], probabilities)
-    return L_tm, torch.from_numpy(N_paths)
+    return L_tm, (torch.from_numpy(N_paths[::reduction]).to(torch.float64) / params['N']).to(device)
 
 
 def _run(params, model, sim_params):
@@ -79,9 +90,8 @@ def _run(params, model, sim_params):
     reduction = floor((n_time_steps - 1) / (T / rebalancing)) ; print(f'reduction = {reduction}')
 
     Y_tm, Y_T = _simulate_common(params, model, sim_params, n_time_steps, reduction, device)
-    L_tm, N_paths = _mortality(params, n_time_steps, dt, device)
+    L_tm, N_NN = _mortality(params, n_time_steps, dt, reduction, device)      # N_paths / N at the kept columns
     B = bond_curve(r, T, n_time_steps, reduction)
-    N_red = N_paths[::reduction]                                   # (n_red, paths)
     n_red = Y_tm.shape[0]
     dt_red = dt * reduction
 
@@ -89,7 +99,6 @@ def _run(params, model, sim_params):
     sums, otm = payoff_sums(Y_T.unsqueeze(0).contiguous(), [K], [0], kind='floor', s0=Y)
     n_paths = Y_tm.shape[1]
     out_of_money_P = float(otm[0]) / n_paths
-    N_NN = (N_red.to(torch.float64) / N).to(device)                # N_paths / N
     Payoff_Y = torch.where(Y_T > K, Y_T, torch.full_like(Y_T, float(K)))
     terminal = (Payoff_Y * N_NN[-1]).to(torch.float32)
 

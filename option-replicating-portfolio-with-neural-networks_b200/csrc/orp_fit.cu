@@ -1059,11 +1059,16 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_residual_kernel(const FitA
     }
 }
 
+// Fixed-order sum of the per-block partials: warp k owns quantity k, lane l adds blocks l, l + 32, ... in
+// increasing order, then a shuffle tree — independent loads instead of one chain of 512 dependent ones.
 __global__ void predict_reduce_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ sums) {
-    if (threadIdx.x >= 4) return;
+    const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (k >= 4) return;
     double t = 0.0;
-    for (int b = 0; b < n_blocks; ++b) t += partials[(size_t)b * 4 + threadIdx.x];
-    sums[threadIdx.x] = t;
+    for (int b = lane; b < n_blocks; b += 32) t += partials[(size_t)b * 4 + k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+    if (lane == 0) sums[k] = t;
 }
 
 // ---- Keras-faithful mini-batch epoch: one block, serial over batches ------------------------------
@@ -1392,7 +1397,7 @@ extern "C" int orp_fit_predict(const orp_fit_batch* b, const float* d_params, fl
         else     fit_predict_kernel<ORP_NET_RP, float><<<grid, kFitThreads, 0, st>>>(a, d_params, d_values_out, partials);
     }
     ORP_LAUNCH_CHECK("fit_predict_kernel");
-    predict_reduce_kernel<<<1, 32, 0, st>>>(partials, grid, d_sums);
+    predict_reduce_kernel<<<1, 128, 0, st>>>(partials, grid, d_sums);
     ORP_LAUNCH_CHECK("predict_reduce_kernel");
     return ORP_OK;
 }

@@ -91,3 +91,26 @@ def quantiles(x, qs, group=None) -> np.ndarray:
                     b = _key_to_float(nxt)
             out[j] = a + (b - a) * g if g < 0.5 else b - (b - a) * (1.0 - g)     # numpy's _lerp
     return out
+
+
+def survivors(lambda_tm, n0: float, dt: float, keep_every: int = 1, seed: int = 1234, start: int = 0):
+    """Per-path binomial survivors ``N_t / N`` on the device (``Replicating_Portfolio.py:78-84``): ``lambda_tm`` is the
+    TIME-MAJOR ``(n_steps + 1, count)`` mortality-intensity array (``simulate_paths('linear', ...)``); returns the fp32
+    ``(n_steps // keep_every + 1, count)`` array of ``N_t / n0`` at the kept columns.  Counter-based draws
+    (Philox4x32-10 indexed by global path ``start + j`` and step): independent of the sharding, distributional — not
+    bit-wise — parity with the reference's NumPy legacy stream."""
+    torch = _lib.require_cuda()
+    if lambda_tm.dim() != 2 or not lambda_tm.is_contiguous():
+        raise ValueError("lambda_tm must be the contiguous time-major (n_steps + 1, count) tensor")
+    if lambda_tm.dtype not in (torch.float64, torch.float32):
+        raise ValueError("lambda_tm must be float64 or float32")
+    n_cols, count = lambda_tm.shape
+    n_steps = n_cols - 1
+    if n_steps < 1 or keep_every < 1:
+        raise ValueError("need at least one step and keep_every >= 1")
+    out = torch.empty((n_steps // keep_every + 1, count), dtype=torch.float32, device=lambda_tm.device)
+    with torch.cuda.device(lambda_tm.device):
+        _lib.check(_lib.lib().orp_survivors(_lib.ptr(lambda_tm), _lib.F64 if lambda_tm.dtype == torch.float64 else _lib.F32,
+                                            count, int(start), count, n_steps, int(keep_every), float(n0), float(dt),
+                                            int(seed), _lib.ptr(out), count, _lib.stream_ptr()))
+    return out

@@ -55,3 +55,10 @@ def test_replicating_portfolio_sv_dropin_notebook_call(cuda):
     import Replicating_Portfolio as RP
     phi, psi = RP.Replicating_Portfolio_SV(dict(SV_PARAMETERS, verbose=False))
     _check(phi, psi, 626_123, 371_854)
+
+
+def test_replicating_portfolio_dropin_with_device_survivors(cuda):
+    """Same call with the survivors drawn on the GPU (the route taken beyond 2^16 paths): same tolerances."""
+    import Replicating_Portfolio as RP
+    phi, psi = RP.Replicating_Portfolio(dict(PARAMETERS, verbose=False, survivors='device'))
+    _check(phi, psi, 634_349, 350_176)
