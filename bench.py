@@ -306,7 +306,9 @@ def run_own(args):
         "roofline": {"kernel": "paths_kernel<GBM_LOG,double>", "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
                      "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": profiled_traffic(m, D) if world == 1 else None,
                      "peak_kind": peak_kind + " (burst copy figure)",
-                     "algorithmic_bytes_per_launch": path_bytes, "ms_per_launch": t_paths},
+                     "algorithmic_bytes_per_launch": path_bytes, "ms_per_launch": t_paths,
+                     "note": "north_star's HBM-bound kernel; by TIME the step is dominated by the fit kernel, which is bound by the "
+                             "fp32 FMA pipe (width-8 layers: SIMT by north_star's own rule), see fit_kernel"},
         "fit_kernel": {"kernel": "fit_run_kernel<EO,MSE,double> (persistent, one launch per Model.fit)", "bound": "fp32 FMA pipe (packed FFMA2), not hbm/tensor: width-8 layers",
                        "tflops": fit_flops / (t_fit * 1e-3) / 1e12, "peak_nominal_tflops": FP32_NOMINAL_TFLOPS,
                        "epochs_per_step": epochs, "samples_per_s_per_gpu": 2 ** m / world * epochs / (t_fit * 1e-3),
