@@ -205,7 +205,9 @@ int orp_fit_epochs(const orp_fit_batch* parts, int n_parts, float* d_params, dou
  * block per SM stays resident, synchronises once per step with a grid barrier, and every block applies the same
  * fixed-order reduction and Adam step to its own copy of the weights.  Runs at most n_epochs epochs and returns to
  * the host as soon as EarlyStopping fires.  Results are bit-identical to orp_fit_grad -> orp_fit_update.
- * Needs a device that supports cooperative launches (every B200 does). */
+ * d_scratch (orp_fit_scratch_bytes()) must be ZERO-FILLED once before its first use and then left alone between
+ * calls: blocks hand their totals to each other through entries tagged with a step counter kept in it (no grid-wide
+ * barrier).  Needs a device that supports cooperative launches (every B200 does): all blocks must be co-resident. */
 int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
                 void* d_scratch, int n_epochs, void* stream);
 

@@ -464,9 +464,21 @@ __device__ __forceinline__ int scattered_index(int i, int lane) {
 // Block total of the per-thread gradients, loss and sample count as ONE fp64 vector: warp reduce-scatter ->
 // shared memory -> sum over the 8 warps in warp order -> dst[index * stride] (index = k for the gradient of
 // parameter k, ORP_FIT_MAX_PARAMS for the loss, + 1 for the count).  Shared by every driver of the fit.
+// tag != 0: every entry is written as two 8-byte words {low half, tag}, {high half, tag} (dst counts 16-byte
+// entries), so that a reader polling for `tag` needs no barrier and no fence (8-byte stores are single-copy atomic).
+__device__ __forceinline__ void st_tagged(double* entry, double val, unsigned int tag) {
+    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(entry), "r"((unsigned int)__double2loint(val)), "r"(tag),
+                 "r"((unsigned int)__double2hiint(val)), "r"(tag) : "memory");
+}
+__device__ __forceinline__ uint4 ld_tagged(const double* entry) {
+    uint4 v;
+    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(entry) : "memory");
+    return v;
+}
+
 template <int NET>
 __device__ __forceinline__ void block_partial(const Grads<NET>& g, float loss, uint32_t n, float (&s_red)[kFitThreads / 32][Net<NET>::P + 2],
-                                              double* __restrict__ dst, size_t stride) {
+                                              double* __restrict__ dst, size_t stride, unsigned int tag = 0u) {
     constexpr int P = Net<NET>::P;
     constexpr int N = P + 2;
     constexpr int NB = (N % 32) <= 4 ? (N / 32) * 32 : ((N + 31) / 32) * 32;      // EO: 96 (+ 3 by the classic tree); RP: 128
@@ -493,7 +505,8 @@ __device__ __forceinline__ void block_partial(const Grads<NET>& g, float loss, u
         double t = 0.0;
 #pragma unroll
         for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[w][q];
-        dst[(size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * stride] = t;
+        const size_t at = (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * stride;
+        if (tag) st_tagged(dst + 2 * at, t, tag); else dst[at] = t;
     }
 }
 
@@ -669,40 +682,15 @@ __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
     return v;
 }
 
-// Grid barrier in two halves so that work can sit between "arrive" and "wait".  All threads of all blocks call
-// both.  barrier_wait returns false when the barrier timed out (a block is missing: the launch was not cooperative,
-// or the device is wedged) — every block then leaves the kernel instead of hanging the GPU.
-__device__ __forceinline__ void barrier_arrive(unsigned int* arrivals) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        atomicAdd(arrivals, 1u);
-    }
-}
-__device__ __forceinline__ bool barrier_wait(unsigned int* arrivals, unsigned int* abort_flag, unsigned int target) {
-    __shared__ int s_ok;
-    if (threadIdx.x == 0) {
-        int ok = 1;
-        unsigned int spins = 0;
-        while (ld_acquire_u32(arrivals) < target) {
-            if (++spins > (1u << 26) || ld_acquire_u32(abort_flag) != 0u) { atomicExch(abort_flag, 1u); ok = 0; break; }
-        }
-        __threadfence();
-        s_ok = ok;
-    }
-    __syncthreads();
-    return s_ok != 0;
-}
-
 // Optional phase timestamps (build with -DORP_FIT_TRACE; tools/trace_fit.py): blocks 0 and G-1 write %globaltimer at
-// eight points of each of the first 512 optimiser steps into the unused tail of the scratch buffer.
+// eight points of each of the first 512 optimiser steps into the 64 KB tail of the scratch buffer.
 #ifdef ORP_FIT_TRACE
 #define ORP_TRACE(phase)                                                                                          \
     do {                                                                                                          \
         if (threadIdx.x == 0 && (blockIdx.x == 0 || blockIdx.x == gridDim.x - 1) && barriers_done_for_trace < 512) { \
             unsigned long long t_;                                                                                \
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));                                                \
-            reinterpret_cast<unsigned long long*>(partials)[(600 * 1024) / 8 +                                     \
+            reinterpret_cast<unsigned long long*>(partials)[kScrDoubles +                                          \
                 ((blockIdx.x == 0 ? 0 : 512) + barriers_done_for_trace) * 8 + (phase)] = t_;                     \
         }                                                                                                         \
     } while (0)
@@ -732,9 +720,18 @@ struct RunArgs {
 // s + 1, i.e. after all of that peer's blocks have finished reading step s.
 constexpr int kPeerMaxWorld = 16;
 constexpr int kPeerHdr = 0;                                     // word 0 (uint32): optimiser steps completed so far
-constexpr int kPeerSlots = 32;                                  // uint2 slots[2][kPeerMaxWorld][2 * kGsumLen], in 8-byte words
+constexpr int kPeerSlots = 32;                                  // tagged totals [2][kPeerMaxWorld][kGsumLen][2], in 8-byte words
 constexpr int kPeerSlotWords = 2 * kGsumLen;
 constexpr int kPeerDoubles = kPeerSlots + 2 * kPeerMaxWorld * kPeerSlotWords;
+
+// Scratch layout of the persistent fit (in doubles from the start of d_scratch; the first region belongs to the
+// per-step drivers).  The scratch must be ZERO-FILLED once before its first use: the tags below count up from the
+// step counter kept in its header and must never meet stale memory that happens to carry a future tag.
+constexpr int kLLBlocks = 512;                                              // grid size limit (fit_blocks caps at 512)
+constexpr size_t kScrHeader = 512ull * kGsumLen;                            // word 0 (uint32): optimiser steps done with this scratch
+constexpr size_t kScrLLPart = kScrHeader + 16;                              // tagged block totals [2][kGsumLen][kLLBlocks][2]
+constexpr size_t kScrLLFinal = kScrLLPart + 2ull * kGsumLen * kLLBlocks * 2;    // tagged totals [2][kPeerMaxWorld][kGsumLen][2] (one GPU)
+constexpr size_t kScrDoubles = kScrLLFinal + 2ull * kPeerMaxWorld * kGsumLen * 2;
 
 __device__ __forceinline__ void st_ll(double* word, unsigned int data, unsigned int flag) {
     asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(word), "r"(data), "r"(flag) : "memory");
@@ -776,8 +773,6 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     __shared__ int s_improved;
     __shared__ double s_num[kFitThreads], s_den[kFitThreads];      // Adam bias terms of the next 256 steps
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    unsigned int* arrivals = reinterpret_cast<unsigned int*>(state + ST_BARRIER);
-    unsigned int* exits = arrivals + 1;
     unsigned int* abort_flag = reinterpret_cast<unsigned int*>(state + ST_ABORT);
 
     load_weights<NET>(s_w, params, tid, kFitThreads);
@@ -790,8 +785,13 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     unsigned int barriers = 0;
     bool alive = true;
     __shared__ int s_peer_ok;
+    double* const ll_part = partials + kScrLLPart;                                     // tagged block totals
+    double* const ll_final = partials + kScrLLFinal;                                   // tagged totals, single-GPU form
     double* const xbuf = r.world > 0 ? r.peers[r.rank] : nullptr;                      // this GPU's exchange buffer
-    const unsigned int step0 = r.world > 0 ? *reinterpret_cast<const unsigned int*>(xbuf + kPeerHdr) : 0u;
+    const int n_ranks = r.world > 0 ? r.world : 1, my_rank = r.world > 0 ? r.rank : 0;
+    const double* const fin_mine = r.world > 0 ? xbuf + kPeerSlots : ll_final;         // where the ranks' totals arrive
+    const unsigned int tag0 = *reinterpret_cast<const unsigned int*>(partials + kScrHeader);    // steps done with this scratch
+    const unsigned int step0 = r.world > 0 ? *reinterpret_cast<const unsigned int*>(xbuf + kPeerHdr) : tag0;
 
     RawSample<NET, T> first[kFitUnroll<NET>];
     {
@@ -816,28 +816,28 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, g_k, first, g, loss, n);
             ORP_TRACE(1);
 
-            // ---- block reduction -> partials[parity][k][block]
-            double* part = partials + (size_t)(barriers & 1u) * kGsumLen * G;
-            block_partial<NET>(g, loss, n, s_red, part + blockIdx.x, G);
-            // request the first tile of the NEXT optimiser step now: the loads land while the block sits in the barrier
-            // and the reduction (wasted only when the fit stops here)
+            // ---- block total -> tagged entry [parity][column][block] (blocks without tiles in this batch publish nothing)
+            ++barriers;
+            const unsigned int tag = tag0 + barriers;                          // never 0; grows across launches
+            const unsigned int par = tag & 1u;
+            double* const part = ll_part + (size_t)par * kGsumLen * kLLBlocks * 2;
+            if (blockIdx.x < g_k) block_partial<NET>(g, loss, n, s_red, part + 2 * blockIdx.x, kLLBlocks, tag);
+            // request the first tile of the NEXT optimiser step now: the loads land while this block waits for the
+            // other blocks' totals (wasted only when the fit stops here)
             {
                 uint32_t g_next;
                 const FitArgs a_next = part_args<T>(r, k + 1 < r.n_parts ? k + 1 : 0, G, g_next);
                 load_first_tile<NET, T>(a_next, blockIdx.x, first);
             }
             ORP_TRACE(2);
-            ++barriers;
-            barrier_arrive(arrivals);
-            ORP_TRACE(3);
-            // between arrive and wait: the step's learning rate.  Its two double pow() per step come from a table that
-            // all threads refill together every 256 steps (thread i: step t + i), so they stay off the critical path.
+            // the step's learning rate: Adam bias terms from a table that all threads refill together every 256 steps
             if (((barriers - 1u) & (kFitThreads - 1u)) == 0u) {
                 const double ti = s_c[ST_ADAM_T] + 1.0 + (double)tid;
                 s_num[tid] = sqrt(1.0 - pow(0.999, ti));
                 s_den[tid] = 1.0 - pow(0.9, ti);
-                __syncthreads();
             }
+            if (tid == 0) s_peer_ok = 1;
+            __syncthreads();
             if (tid == 32) {
                 double lr = s_c[ST_LR];
                 if (k == 0 && s_c[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)s_c[ST_EPOCH], lr);
@@ -846,88 +846,99 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 const unsigned int i = (barriers - 1u) & (kFitThreads - 1u);
                 s_lr_t = (float)(lr * s_num[i] / s_den[i]);
             }
-            alive = barrier_wait(arrivals, abort_flag, barriers * G);
-            ORP_TRACE(4);
-            if (!alive) break;
+            ORP_TRACE(3);
 
-            // ---- fixed-order sum over this GPU's blocks (same association as fit_reduce_kernel): every block when
-            //      there is one GPU, block 0 alone when the ranks exchange their sums
-            if (r.world == 0 || blockIdx.x == 0) {
-                constexpr int NQ = (P + 2 + 7) / 8;                             // columns per warp: q = warp, warp + 8, ...
-                constexpr int NJ = 5;                                           // 5 x 32 blocks per pass
-                double t[NQ];
+            // ---- column owners: column q belongs to block q mod G (one warp each).  The owner polls the g_k tagged
+            //      entries of its column (no barrier: the tag says "this step"), adds them in the fixed order of
+            //      fit_reduce_kernel (lane l: blocks l, l + 32, ...; then a shuffle tree) and publishes the total, again
+            //      tagged, in slot [parity][rank][column] of every rank — its own memory when there is one GPU,
+            //      plain stores over NVLink to the peers' mapped buffers otherwise.
+            const unsigned int step_id = step0 + barriers;                    // tag of the published totals: same on every rank
+            const unsigned int fpar = step_id & 1u;
+            // (owners are taken from the TOP of the grid: when the tiles do not divide evenly the low-numbered blocks carry
+            //  the extra tile and finish last — they should not also have a column to add up)
+            for (int q = (int)(G - 1 - blockIdx.x) + warp * (int)G; q < P + 2; q += 8 * (int)G) {
+                const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
+                const double* col = part + (size_t)qq * kLLBlocks * 2;
+                double t = 0.0;
+                bool ok = true;
+                for (uint32_t b0 = 0; b0 < g_k && ok; b0 += 160) {
+                    // every retry re-reads ALL of this lane's entries at once (independent loads: one L2 round trip per
+                    // retry), so the total is ready at most two round trips after the last block has published
+                    uint4 v[5];
+                    unsigned int spins = 0;
+                    for (;;) {
+                        bool ready = true;
 #pragma unroll
-                for (int u = 0; u < NQ; ++u) t[u] = 0.0;
-                for (uint32_t b0 = 0; b0 < g_k; b0 += 32 * NJ) {
-                    // all NQ x NJ loads are issued before the first add: one L2 round trip, not one per group
-                    double v[NJ][NQ];
+                        for (int j = 0; j < 5; ++j) v[j] = ld_tagged(col + 2 * (size_t)min(b0 + 32 * j + lane, g_k - 1));
 #pragma unroll
-                    for (int j = 0; j < NJ; ++j) {
-                        const uint32_t b = min(b0 + 32 * j + lane, g_k - 1);    // clamped: out-of-range lanes re-read a valid entry
-#pragma unroll
-                        for (int u = 0; u < NQ; ++u) {
-                            const int q = min(warp + 8 * u, P + 1);
-                            v[j][u] = __ldcg(part + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * G + b);
-                        }
+                        for (int j = 0; j < 5; ++j) ready = ready && v[j].y == tag && v[j].w == tag;
+                        if (ready) break;
+                        if (++spins > (1u << 22) || (((spins & 255u) == 0u) && ld_acquire_u32(abort_flag) != 0u)) { ok = false; break; }
                     }
 #pragma unroll
-                    for (int j = 0; j < NJ; ++j) {
-                        const bool in = b0 + 32 * j + lane < g_k;
-#pragma unroll
-                        for (int u = 0; u < NQ; ++u) t[u] += in ? v[j][u] : 0.0;      // same order as fit_reduce_kernel: b ascending
-                    }
+                    for (int j = 0; j < 5; ++j) t += b0 + 32 * j + lane < g_k ? __hiloint2double((int)v[j].z, (int)v[j].x) : 0.0;
                 }
+                ok = __all_sync(0xffffffffu, ok);
 #pragma unroll
-                for (int u = 0; u < NQ; ++u) {
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) t[u] += __shfl_down_sync(0xffffffffu, t[u], o);
-                    const int q = warp + 8 * u;
-                    if (lane == 0 && q < P + 2) s_g[q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)] = t[u];
+                for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+                if (!ok) { if (lane == 0) { atomicExch(abort_flag, 1u); s_peer_ok = 0; } continue; }
+                t = __shfl_sync(0xffffffffu, t, 0);
+                if (lane < n_ranks) {
+                    double* dst = (r.world > 0 ? r.peers[lane] + kPeerSlots : ll_final)
+                                  + (((size_t)fpar * kPeerMaxWorld + my_rank) * kGsumLen + qq) * 2;
+                    st_tagged(dst, t, step_id);
+                }
+            }
+            ORP_TRACE(4);
+            // ---- every block: wait for the ranks' totals in its OWN GPU's memory and add them in rank order (same bits
+            //      everywhere).  ONE thread per block watches one entry (a different column per block, so the watchers
+            //      spread over the cache lines) with a back-off; a column total can only exist once every block has
+            //      published, so when it shows up the other columns are at most a fraction of a microsecond behind and the
+            //      per-entry polls below are short.  (148 x 99 threads spinning on 13 cache lines slowed the stragglers down.)
+            if (tid == 0) {
+                const int qg = (int)(blockIdx.x % (unsigned)(P + 2));
+                const int qq = qg < P ? qg : ORP_FIT_MAX_PARAMS + (qg - P);
+                const double* w = fin_mine + (((size_t)fpar * kPeerMaxWorld + (n_ranks - 1)) * kGsumLen + qq) * 2;
+                unsigned int spins = 0;
+                uint4 v = ld_tagged(w);
+                while (v.y != step_id || v.w != step_id) {
+                    if (++spins > (1u << 22) || (((spins & 255u) == 0u) && ld_acquire_u32(abort_flag) != 0u)) break;     // the polls below report it
+                    v = ld_tagged(w);
                 }
             }
             __syncthreads();
-            ORP_TRACE(5);
-            if (r.world > 0) {
-                const unsigned int step_id = step0 + barriers;                 // the same number on every rank, never 0
-                const unsigned int par = step_id & 1u;
-                if (blockIdx.x == 0) {
-                    // send: {low half, step} and {high half, step} of every entry into slot [par][rank] of every rank
-                    for (int idx = tid; idx < (P + 2) * r.world; idx += kFitThreads) {
-                        const int dst = idx / (P + 2), q = idx - dst * (P + 2);
-                        const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
-                        const double val = s_g[qq];
-                        double* w = r.peers[dst] + kPeerSlots + ((size_t)par * kPeerMaxWorld + r.rank) * kPeerSlotWords + 2 * qq;
-                        st_ll(w, (unsigned int)__double2loint(val), step_id);
-                        st_ll(w + 1, (unsigned int)__double2hiint(val), step_id);
-                    }
-                }
-                // receive (every block, from its own GPU's memory): poll until both words of an entry carry this step,
-                // then add the ranks' values in rank order: bit-identical on every GPU
-                if (tid == 0) s_peer_ok = 1;
-                __syncthreads();
-                for (int q = tid; q < P + 2; q += kFitThreads) {
-                    const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
-                    double t = 0.0;
-                    for (int src = 0; src < r.world; ++src) {
-                        const double* w = xbuf + kPeerSlots + ((size_t)par * kPeerMaxWorld + src) * kPeerSlotWords + 2 * qq;
-                        uint2 lo = ld_ll(w), hi = ld_ll(w + 1);
-                        unsigned int spins = 0;
-                        while (lo.y != step_id || hi.y != step_id) {
-                            if (++spins > (1u << 24) || (((spins & 1023u) == 0u) && ld_acquire_u32(abort_flag) != 0u)) {
-                                atomicExch(abort_flag, 1u);
-                                s_peer_ok = 0;
-                                break;
-                            }
-                            lo = ld_ll(w);
-                            hi = ld_ll(w + 1);
+            for (int q = tid; q < P + 2; q += kFitThreads) {
+                const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
+                const double* w0 = fin_mine + ((size_t)fpar * kPeerMaxWorld * kGsumLen + qq) * 2;
+                double t = 0.0;
+                for (int s0 = 0; s0 < n_ranks; s0 += 8) {                      // eight ranks per pass, all their entries per retry
+                    uint4 v[8];
+                    unsigned int spins = 0;
+                    for (;;) {
+                        bool ready = true;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (s0 + j < n_ranks) v[j] = ld_tagged(w0 + (size_t)(s0 + j) * kGsumLen * 2);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j)
+                            if (s0 + j < n_ranks) ready = ready && v[j].y == step_id && v[j].w == step_id;
+                        if (ready) break;
+                        if (++spins > (1u << 22) || (((spins & 255u) == 0u) && ld_acquire_u32(abort_flag) != 0u)) {
+                            atomicExch(abort_flag, 1u);
+                            s_peer_ok = 0;
+                            break;
                         }
-                        t += __hiloint2double((int)hi.x, (int)lo.x);
                     }
-                    s_g[qq] = t;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (s0 + j < n_ranks) t += __hiloint2double((int)v[j].z, (int)v[j].x);       // rank order: same bits on every GPU
                 }
-                __syncthreads();
-                if (!s_peer_ok) { alive = false; break; }
+                s_g[qq] = t;
             }
+            __syncthreads();
+            ORP_TRACE(5);
+            if (!s_peer_ok) { alive = false; break; }
 
             ORP_TRACE(6);
             // ---- Adam step on the block's own copy (identical in every block)
@@ -969,7 +980,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
         }
     }
 
-    // ---- write back (block 0), then the last block out resets the barrier words for the next launch
+    // ---- write back (block 0)
     __syncthreads();
     if (blockIdx.x == 0) {
         if (tid < P) {
@@ -980,12 +991,10 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
         }
         if (tid < 16) state[tid] = s_c[tid];
         for (int q = tid; q < kGsumLen; q += kFitThreads) gsum[q] = s_g[q];
-        if (tid == 0 && r.world > 0) *reinterpret_cast<unsigned int*>(xbuf + kPeerHdr) = step0 + barriers;
-    }
-    __syncthreads();
-    if (tid == 0) {
-        __threadfence();
-        if (atomicAdd(exits, 1u) == G - 1) { *arrivals = 0u; *exits = 0u; }
+        if (tid == 0) {
+            *reinterpret_cast<unsigned int*>(partials + kScrHeader) = tag0 + barriers;
+            if (r.world > 0) *reinterpret_cast<unsigned int*>(xbuf + kPeerHdr) = step0 + barriers;
+        }
     }
 }
 
@@ -1202,7 +1211,7 @@ extern "C" int orp_fit_n_params(int net) {
     return net == ORP_NET_EO ? Net<ORP_NET_EO>::P : net == ORP_NET_RP ? Net<ORP_NET_RP>::P : -1;
 }
 
-extern "C" uint64_t orp_fit_scratch_bytes(void) { return 2ull * 512ull * kGsum * sizeof(double); }   // two parities (persistent fit)
+extern "C" uint64_t orp_fit_scratch_bytes(void) { return kScrDoubles * sizeof(double) + 65536; }   // + tail for the optional phase trace
 
 #define ORP_FIT_DISPATCH(KERNEL_CALL)                                                              \
     do {                                                                                           \

@@ -81,7 +81,8 @@ class ReplicationNet:
         self.params = torch.zeros(_lib.FIT_MAX_PARAMS, dtype=torch.float32, device=self.device)
         self.params[:self.P] = torch.from_numpy(np.ascontiguousarray(params0, dtype=np.float32)).to(self.device)
         self.gsum = torch.zeros(_lib.GSUM_LEN, dtype=torch.float64, device=self.device)
-        self.scratch = torch.empty(_lib.lib().orp_fit_scratch_bytes(), dtype=torch.uint8, device=self.device)
+        # zero-filled: the persistent kernel's hand-offs are tagged with a step counter kept in this buffer
+        self.scratch = torch.zeros(_lib.lib().orp_fit_scratch_bytes(), dtype=torch.uint8, device=self.device)
         self.sums = torch.zeros(4, dtype=torch.float64, device=self.device)
         self.launches = 0
         self.two_stage = False      # True forces grad -> [all-reduce] -> update even on one GPU (tests, multi-GPU form)

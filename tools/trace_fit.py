@@ -25,8 +25,8 @@ for rep in range(2):
     mdl.scratch.zero_()
     mdl.fit(b, opt, epochs=40, patience=1000, use_schedule=False, steps_per_epoch=parts)
 torch.cuda.synchronize()
-raw = mdl.scratch.cpu().numpy().view(np.uint64)[600 * 1024 // 8:600 * 1024 // 8 + 2 * 512 * 8].reshape(2, 512, 8).astype(np.float64)
-names = ["accumulate", "block reduce + partial + prefetch", "arrive", "lr + wait", "cross-block sum", "exchange", "adam + callbacks"]
+raw = mdl.scratch.cpu().numpy()[-65536:].view(np.uint64)[:2 * 512 * 8].reshape(2, 512, 8).astype(np.float64)
+names = ["accumulate", "block total + prefetch", "lr", "own column: poll + sum + publish", "poll totals", "(sync)", "adam + callbacks"]
 n_steps = min(512, 40 * parts)
 for blk, label in ((0, "block 0"), (1, "block G-1")):
     t = raw[blk, 8:n_steps]                                   # skip the first steps (cold)
