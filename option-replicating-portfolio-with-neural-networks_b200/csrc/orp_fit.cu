@@ -19,8 +19,8 @@ enum {
     ST_STOPPED_EARLY, ST_LAST_LOSS, ST_EPOCHS_RUN, ST_HAVE_BEST, ST_TOTAL_EPOCHS, ST_LOSS_ACC, ST_COUNT_ACC,
     ST_ADAM_M = 16, ST_ADAM_V = ST_ADAM_M + ORP_FIT_MAX_PARAMS, ST_BEST_W = ST_ADAM_V + ORP_FIT_MAX_PARAMS,
     ST_TICKET = ST_BEST_W + ORP_FIT_MAX_PARAMS,      // block-arrival counter of the single-launch step (used as uint32)
-    ST_BARRIER,                                      // persistent kernel: grid-barrier arrivals (uint32) | exits (uint32)
-    ST_ABORT,                                        // persistent kernel: non-zero when a grid barrier timed out (uint32)
+    ST_SPARE,                                        // (unused)
+    ST_ABORT,                                        // persistent kernel: non-zero when a hand-over poll timed out (uint32)
     ST_END
 };
 static_assert(ST_END <= ORP_FIT_STATE_DOUBLES, "state block too small");
@@ -669,13 +669,14 @@ __global__ void fit_end_kernel(int P, float* __restrict__ params, double* __rest
 
 // ---- persistent fit: every epoch of a Model.fit call in ONE cooperative launch ----------------------
 //
-// One block per SM stays resident for the whole fit.  Per optimiser step: each block accumulates its tiles of the
-// batch, reduces to one fp64 partial (stored [parity][k][block], so the cross-block read is coalesced), passes
-// a grid barrier, then EVERY block adds the partials in the same fixed order and applies the Adam step to its own
-// shared-memory copy of the weights (moments in registers, callback state in shared memory): all blocks hold
-// bit-identical weights and take identical decisions, so no second barrier and no weight round trip through
-// global memory are needed.  Block 0 writes weights and state back when the fit stops or the epochs run out.
-// Per-step fixed cost: one block reduction + one barrier (~2 us) instead of a kernel boundary (~18 us measured).
+// One block per SM stays resident for the whole fit (cooperative launch: all blocks co-resident).  Per optimiser
+// step: each block accumulates its tiles of the batch and reduces them to one fp64 vector, which it publishes as
+// tagged entries [parity][column][block]; the owner block of each column adds the blocks' entries in the fixed order
+// of fit_reduce_kernel and publishes the column total (to every rank); EVERY block then adds the ranks' totals and
+// applies the Adam step to its own shared-memory copy of the weights (moments in registers, callback state in shared
+// memory).  All blocks hold bit-identical weights and take identical decisions, so there is no grid-wide barrier and no
+// weight round trip through global memory.  Block 0 writes weights and state back when the fit stops or the epochs
+// run out.  Per-step fixed cost: ~5 us instead of a kernel boundary (~18 us measured).
 __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
     unsigned int v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -710,19 +711,17 @@ struct RunArgs {
 };
 
 // ---- exchange buffer of the multi-GPU fit (one per rank, cudaMalloc'ed, mapped into every peer through CUDA IPC) ----
-// The ranks' [gradient, loss, count] vectors are all-gathered by plain stores over NVLink, with the flag travelling
-// INSIDE every 8-byte store (the "LL" idea of collective libraries): a double is sent as two words
-// {low 32 bits, step} and {high 32 bits, step}.  8-byte stores are single-copy atomic, so a receiver that sees
-// the step number it is waiting for in both words has the value — no fence, no separate flag, one NVLink
-// one-way latency.  Block 0 of rank r writes its locally reduced vector into slot [parity][r] of EVERY rank's
-// buffer; every block of every rank polls the `world` slots in its OWN memory and adds them in rank order — the
-// same bits on every GPU.  Two parities suffice: a rank can only send step s + 2 after every peer has sent step
-// s + 1, i.e. after all of that peer's blocks have finished reading step s.
+// The column totals of every rank are all-gathered by plain stores over NVLink with the flag travelling INSIDE the
+// store (the "LL" idea of collective libraries): a double is sent as {low 32 bits, step, high 32 bits, step}.
+// 8-byte halves are single-copy atomic, so a receiver that sees the step number it is waiting for in both halves has
+// the value — no fence, no separate flag, one NVLink one-way latency.  The owner warp of a column writes its total into
+// slot [parity][rank][column] of EVERY rank's buffer; every block of every rank polls the `world` slots in its OWN memory
+// and adds them in rank order — the same bits on every GPU.  Two parities suffice: a rank can only send step s + 2 after
+// every peer has sent step s + 1, i.e. after all of that peer's blocks have finished reading step s.
 constexpr int kPeerMaxWorld = 16;
 constexpr int kPeerHdr = 0;                                     // word 0 (uint32): optimiser steps completed so far
 constexpr int kPeerSlots = 32;                                  // tagged totals [2][kPeerMaxWorld][kGsumLen][2], in 8-byte words
-constexpr int kPeerSlotWords = 2 * kGsumLen;
-constexpr int kPeerDoubles = kPeerSlots + 2 * kPeerMaxWorld * kPeerSlotWords;
+constexpr int kPeerDoubles = kPeerSlots + 2 * kPeerMaxWorld * kGsumLen * 2;
 
 // Scratch layout of the persistent fit (in doubles from the start of d_scratch; the first region belongs to the
 // per-step drivers).  The scratch must be ZERO-FILLED once before its first use: the tags below count up from the
@@ -732,15 +731,6 @@ constexpr size_t kScrHeader = 512ull * kGsumLen;                            // w
 constexpr size_t kScrLLPart = kScrHeader + 16;                              // tagged block totals [2][kGsumLen][kLLBlocks][2]
 constexpr size_t kScrLLFinal = kScrLLPart + 2ull * kGsumLen * kLLBlocks * 2;    // tagged totals [2][kPeerMaxWorld][kGsumLen][2] (one GPU)
 constexpr size_t kScrDoubles = kScrLLFinal + 2ull * kPeerMaxWorld * kGsumLen * 2;
-
-__device__ __forceinline__ void st_ll(double* word, unsigned int data, unsigned int flag) {
-    asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(word), "r"(data), "r"(flag) : "memory");
-}
-__device__ __forceinline__ uint2 ld_ll(const double* word) {
-    uint2 v;
-    asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(word) : "memory");
-    return v;
-}
 
 // Batch k of the epoch and the number of blocks that work on it (the grid orp_fit_grad would launch for it).
 template <typename T>

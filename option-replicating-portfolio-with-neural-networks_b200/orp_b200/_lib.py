@@ -32,8 +32,7 @@ ST_ADAM_M = 16
 ST_ADAM_V = ST_ADAM_M + FIT_MAX_PARAMS
 ST_BEST_W = ST_ADAM_V + FIT_MAX_PARAMS
 ST_TICKET = ST_BEST_W + FIT_MAX_PARAMS
-ST_BARRIER = ST_TICKET + 1
-ST_ABORT = ST_BARRIER + 1
+ST_ABORT = ST_TICKET + 2
 
 
 class PathParams(C.Structure):

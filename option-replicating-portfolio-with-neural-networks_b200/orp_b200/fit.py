@@ -214,7 +214,7 @@ class ReplicationNet:
                 self.launches += 1
                 done = epochs
             elif single_launch and self.persistent:
-                # one process, one GPU: the whole epoch loop is ONE cooperative launch (grid barrier per optimiser step);
+                # one process, one GPU: the whole epoch loop is ONE cooperative launch (tagged hand-overs between blocks);
                 # the kernel leaves as soon as EarlyStopping fires, so there is nothing to poll
                 _lib.check(L.orp_fit_run(C.byref(batch), int(steps_per_epoch), _lib.ptr(self.params), _lib.ptr(opt.state),
                                          _lib.ptr(self.gsum), _lib.ptr(self.scratch), int(epochs), st))
@@ -262,7 +262,7 @@ class ReplicationNet:
             self.launches += 2
             h = opt.head()
             if h[-1] != 0.0:
-                raise RuntimeError("orp_fit_run: a grid barrier timed out (the cooperative grid was not fully resident); "
+                raise RuntimeError("orp_fit_run: a hand-over between thread blocks (or ranks) timed out; "
                                    "the optimiser state is unusable — create a new Optimizer")
         return {"epochs_run": int(h[_lib.ST_EPOCHS_RUN]), "loss": float(h[_lib.ST_LAST_LOSS]),
                 "stopped_early": bool(h[_lib.ST_STOPPED_EARLY]), "lr": float(h[_lib.ST_LR])}
