@@ -68,3 +68,28 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in text and "from oracle" not in text, f
+
+
+def test_cir_calibration_matches_the_reference_regression():
+    """estimate_CIR_params against the reference's formulation (scikit-learn's
+    LinearRegression(fit_intercept=False), Extra notebook cell 4) on a synthetic volatility series, and the
+    CIRParams validity check (cell 3)."""
+    import pytest
+    from sklearn.linear_model import LinearRegression
+    from orp_b200 import CIRParams, estimate_CIR_params
+    rng = np.random.default_rng(3)
+    a, b, c, n = 0.02, 0.16, 0.004, 4000
+    s = np.empty(n)
+    s[0] = 0.15
+    for t in range(1, n):                                  # the reference's own recursion (RP.py:285, dt folded in)
+        s[t] = s[t - 1] + a * (b - s[t - 1]) + c * np.sqrt(s[t - 1]) * rng.standard_normal()
+    got = estimate_CIR_params(s)
+    sq = np.sqrt(s[:-1])
+    y, X = np.diff(s) / sq, np.stack([1.0 / sq, sq], axis=1)
+    reg = LinearRegression(fit_intercept=False).fit(X, y)
+    ref_a = -reg.coef_[1]
+    ref = (ref_a, reg.coef_[0] / ref_a, np.std(y - reg.predict(X)))
+    np.testing.assert_allclose([got.a, got.b, got.c], ref, rtol=1e-9)
+    assert abs(got.b - b) < 0.02 and abs(got.c / c - 1) < 0.05
+    with pytest.raises(ValueError, match="2ab"):
+        CIRParams(0.001, 0.1, 0.1)
