@@ -41,24 +41,43 @@ __global__ void __launch_bounds__(kPayThreads) payoff_partial_kernel(const Payof
 #pragma unroll
     for (int k = 0; k < kPayChunk; ++k) sum[k] = otm[k] = 0.0;
 
-    for (uint64_t i = (uint64_t)blockIdx.x * kPayThreads + threadIdx.x; i < a.count; i += (uint64_t)gridDim.x * kPayThreads) {
+    // four paths per thread and iteration: their column loads are independent, so four 8-byte requests per thread are
+    // in flight (one per thread covered a quarter of the bandwidth-delay product of HBM)
+    constexpr int U = 4;
+    const uint64_t stride = (uint64_t)gridDim.x * kPayThreads;
+    for (uint64_t i = (uint64_t)blockIdx.x * kPayThreads + threadIdx.x; i < a.count; i += U * stride) {
         int last_col = -1;
-        double s = 0.0;
+        double s[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) s[u] = 0.0;
 #pragma unroll
         for (int k = 0; k < kPayChunk; ++k) {
             if (k < n_here) {
                 const int col = a.cols[o_first + k];
-                if (col != last_col) { s = (double)paths[(size_t)col * a.ld + i]; last_col = col; }
+                if (col != last_col) {
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        const uint64_t iu = i + u * stride;
+                        s[u] = iu < a.count ? (double)paths[(size_t)col * a.ld + iu] : 0.0;
+                    }
+                    last_col = col;
+                }
                 const double K = a.strikes[o_first + k];
-                double pay, is_otm;
-                if (a.kind == ORP_PAYOFF_CALL)      { pay = fmax(s - K, 0.0); is_otm = pay > 0.0 ? 0.0 : 1.0; }   // EO cell 8
-                else if (a.kind == ORP_PAYOFF_PUT)  { pay = fmax(K - s, 0.0); is_otm = pay > 0.0 ? 0.0 : 1.0; }
-                else                                { pay = s > K ? s : K;    is_otm = s < a.s0 ? 1.0 : 0.0; }    // RP.py:88-89
-                // np.maximum propagates NaN, fmax does not
-                if (a.kind != ORP_PAYOFF_FLOOR && s != s) pay = s;
-                sum[k] += pay;
-                otm[k] += is_otm;
-                if (k == 0 && chunk == 0 && a.values_out) a.values_out[i] = (float)(pay * a.value_scale);
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const uint64_t iu = i + u * stride;
+                    if (iu < a.count) {
+                        double pay, is_otm;
+                        if (a.kind == ORP_PAYOFF_CALL)      { pay = fmax(s[u] - K, 0.0); is_otm = pay > 0.0 ? 0.0 : 1.0; }   // EO cell 8
+                        else if (a.kind == ORP_PAYOFF_PUT)  { pay = fmax(K - s[u], 0.0); is_otm = pay > 0.0 ? 0.0 : 1.0; }
+                        else                                { pay = s[u] > K ? s[u] : K; is_otm = s[u] < a.s0 ? 1.0 : 0.0; } // RP.py:88-89
+                        // np.maximum propagates NaN, fmax does not
+                        if (a.kind != ORP_PAYOFF_FLOOR && s[u] != s[u]) pay = s[u];
+                        sum[k] += pay;
+                        otm[k] += is_otm;
+                        if (k == 0 && chunk == 0 && a.values_out) a.values_out[iu] = (float)(pay * a.value_scale);
+                    }
+                }
             }
         }
     }
