@@ -206,7 +206,11 @@ def run_reference(args):
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(args.m, D), "paths_log2": args.m, "path_steps": D,
                        "note": "each step is a bounded sample of the workload"},
-            "cpu_baseline": {"value": value, "unit": "path-steps/s", "cores": cores, "kind": "port", "sample": r["sample"]},
+            "cpu_baseline": {"value": value, "unit": "path-steps/s", "cores": cores, "kind": "port", "sample": r["sample"],
+                             "host_cores": os.cpu_count(),
+                             "note": "one core on purpose: >99.9 % of the reference's time is its serial chain of 512-sample Adam "
+                                     "steps on 8-wide layers, which more intra-op threads slow down (8 torch threads: 27.7k "
+                                     "path-steps/s against 104k with one on the build host)"},
             "e2e": {"value": value, "unit": "path-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "check": {"V0": r["V0"], "price_mc": r["price_mc"]}}
     print(json.dumps(line))
