@@ -57,14 +57,16 @@ class Optimizer:
     def __init__(self, device):
         torch = _lib.require_cuda()
         self.state = torch.empty(_lib.FIT_STATE_DOUBLES, dtype=torch.float64, device=device)
+        self._head_idx = None
         with torch.cuda.device(device):
             _lib.check(_lib.lib().orp_fit_init(_lib.ptr(self.state), _lib.stream_ptr()))
 
     def head(self) -> np.ndarray:
         """The 16 scalar control words plus (last entry) the barrier-abort flag, in ONE device-to-host copy."""
-        import torch
-        idx = torch.tensor(list(range(16)) + [_lib.ST_ABORT], device=self.state.device)
-        return self.state[idx].cpu().numpy()
+        if self._head_idx is None:
+            import torch
+            self._head_idx = torch.tensor(list(range(16)) + [_lib.ST_ABORT], device=self.state.device)
+        return self.state[self._head_idx].cpu().numpy()
 
 
 class ReplicationNet:
