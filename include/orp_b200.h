@@ -154,11 +154,17 @@ int orp_fit_n_params(int net);
 
 /* One time step of the backward loop (Replicating_Portfolio.py:195-201; European Options.ipynb cell 13 raw 3551-3558).
  * Feature/price columns are read in place from the time-major path array and cast to fp32 as Keras does. */
+/* orp_fit_batch.reserved flag (no counterpart in the reference, opt-in): a sample whose features, prices or target
+ * are not finite takes no part in the fit (no gradient, no loss, not counted), gets NaN as its rolled-back value and
+ * is left out of the predict sums.  With the reference's arithmetic Euler step a single exact-zero Sobol coordinate
+ * (they exist from 2^22 paths on) otherwise turns the whole fit into NaN. */
+#define ORP_FIT_SKIP_NONFINITE 1
+
 typedef struct orp_fit_batch {
     int32_t net;            /* ORP_NET_* */
     int32_t loss;           /* ORP_LOSS_* */
     int32_t paths_dtype;    /* dtype of d_s_t / d_s_t1 */
-    int32_t reserved;
+    int32_t reserved;       /* flags: ORP_FIT_SKIP_NONFINITE (0 = the reference's behaviour: NaN / inf propagate) */
     uint64_t count;         /* local paths */
     const void* d_s_t;      /* S column t   (feature, and price for the roll-back) */
     const void* d_s_t1;     /* S column t+1 (price the fit is scored on) */

@@ -18,7 +18,9 @@ What runs where (reference lines in brackets):
   reduced on the device.
 
 Imports neither TensorFlow nor matplotlib.  Optional keys beyond the reference's: ``mode`` (``'scaled'``
-default, ``'keras'`` = serial batch-512 mini-batches), ``init_seed``, ``device``, ``verbose``, ``survivors``.
+default, ``'keras'`` = serial batch-512 mini-batches), ``init_seed``, ``device``, ``verbose``, ``survivors``,
+``nonfinite`` (``'propagate'`` = the reference's behaviour, default; ``'skip'`` leaves paths that turned NaN / inf —
+exact-zero Sobol coordinates under the arithmetic Euler step, from 2^22 paths on — out of the fits).
 Like the reference, importing the module seeds NumPy's global generator with 1234 [:27].
 """
 from __future__ import annotations
@@ -121,7 +123,8 @@ def _run(params, model, sim_params):
                           out_bias=[1 - out_of_money_P, out_of_money_P], init_seed=params.get('init_seed', 1234),
                           features=features, second_model=True, cost_of_capital=COST_OF_CAPITAL,
                           verbose=False, on_step=progress if chatty else None,
-                          var_quantiles=(.98, .99) if chatty else None, on_step_end=risk if chatty else None)
+                          var_quantiles=(.98, .99) if chatty else None, on_step_end=risk if chatty else None,
+                          skip_nonfinite=params.get('nonfinite', 'propagate') == 'skip')
     phi = np.float64(res['phi0'] * ADJUSTMENT_FACTOR)
     psi = np.float64(res['psi0'] * ADJUSTMENT_FACTOR)
     return phi, psi

@@ -316,6 +316,7 @@ struct FitArgs {
     const void* s_t; const void* s_t1; const float* feat1; const float* feat2; const float* target;
     uint64_t count;
     float inv_scale_f; double inv_scale; float b_t, b_t1;
+    int skip;                  // non-zero: samples with a non-finite input or target take no part (ORP_FIT_SKIP_NONFINITE)
 };
 
 template <typename T>
@@ -534,10 +535,23 @@ __device__ __forceinline__ void load_raw(const FitArgs& a, uint64_t i, RawSample
 }
 
 template <int NET, typename T>
-__device__ __forceinline__ void unpack_raw(const FitArgs& a, const RawSample<NET, T>& r, float (&x)[Net<NET>::IN], float& s_t1) {
+__device__ __forceinline__ bool unpack_raw(const FitArgs& a, const RawSample<NET, T>& r, float (&x)[Net<NET>::IN], float& s_t1, float& y) {
     x[0] = (float)((double)r.s_t * a.inv_scale);          // divide in fp64, then Keras' cast
     s_t1 = (float)((double)r.s_t1 * a.inv_scale);
+    y = r.y;
     if (NET == ORP_NET_RP) { x[1] = r.f1; x[Net<NET>::IN - 1] = r.f2; }
+    if (a.skip) {                                          // opt-in: a non-finite sample is replaced by zeros and reported
+        bool fin = isfinite(s_t1) && isfinite(y);
+#pragma unroll
+        for (int q = 0; q < Net<NET>::IN; ++q) fin = fin && isfinite(x[q]);
+        if (!fin) {
+#pragma unroll
+            for (int q = 0; q < Net<NET>::IN; ++q) x[q] = 0.f;
+            s_t1 = 0.f; y = 0.f;
+            return false;
+        }
+    }
+    return true;
 }
 
 // A block walks tiles of kFitThreads * U consecutive samples (thread t owns samples t, t + 256, ... of the
@@ -582,16 +596,17 @@ __device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa
 #pragma unroll
         for (int u = 0; u < U; u += S) {
             if (base + (uint64_t)u * kFitThreads < a.count) {                 // slot u valid; later slots of the group may not be
-                float x[S][N::IN], s_t1[S], phi[S], psi[S], v[S], dv[S];
+                float x[S][N::IN], s_t1[S], y[S], phi[S], psi[S], v[S], dv[S];
+                bool fin[S];
                 Acts<NET, S> act;
 #pragma unroll
-                for (int s = 0; s < S; ++s) unpack_raw<NET, T>(a, cur[u + s], x[s], s_t1[s]);      // out-of-range slots hold zeros
+                for (int s = 0; s < S; ++s) fin[s] = unpack_raw<NET, T>(a, cur[u + s], x[s], s_t1[s], y[s]);     // out-of-range slots hold zeros
                 net_forward<NET, S>(s_wa, x, s_t1, a.b_t1, act, phi, psi, v);
 #pragma unroll
                 for (int s = 0; s < S; ++s) {
-                    const bool ok = base + (uint64_t)(u + s) * kFitThreads < a.count;
+                    const bool ok = fin[s] && base + (uint64_t)(u + s) * kFitThreads < a.count;
                     float l;
-                    loss_grad<LOSS>(cur[u + s].y, v[s], l, dv[s]);
+                    loss_grad<LOSS>(y[s], v[s], l, dv[s]);
                     if (!ok) { l = 0.f; dv[s] = 0.f; }
                     loss += l;
                     n += ok ? 1u : 0u;
@@ -1017,9 +1032,18 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitAr
             const uint64_t is = i + s * stride;
             if (is < a.count) {
                 const float v1 = fmaf(phi[s], s_t1[s], psi[s] * a.b_t1);      // model.predict(X1): prices at t+1
+                const float tgt = a.target ? a.target[is] : 0.f;
+                bool fin = isfinite(s_t[s]) && isfinite(s_t1[s]) && isfinite(tgt);
+#pragma unroll
+                for (int q = 0; q < N::IN; ++q) fin = fin && isfinite(x[s][q]);
+                if (a.skip && !fin) {
+                    // opt-in: a path with a non-finite feature, price or target stays marked (NaN) and out of the sums
+                    if (values_out) values_out[is] = __int_as_float(0x7fc00000);
+                    continue;
+                }
                 if (values_out) values_out[is] = v0[s];
                 sv += v0[s]; sphi += phi[s]; spsi += psi[s];
-                if (a.target) sae += fabsf(a.target[is] - v1);                // 'mae' metric of model.evaluate(X1, ...)
+                if (a.target) sae += fabsf(tgt - v1);                         // 'mae' metric of model.evaluate(X1, ...)
             }
         }
     }
@@ -1054,7 +1078,14 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_residual_kernel(const FitA
         Acts<NET, 1> act;
         load_sample<NET, T>(a, i, x[0], s_t, s_t1[0]);
         net_forward<NET, 1>(s_wa, x, s_t1, a.b_t1, act, phi, psi, v1);          // features at t, prices at t+1 (X1)
-        resid[i] = a.target[i] - v1[0];
+        float res = a.target[i] - v1[0];
+        if (a.skip) {                                      // opt-in: same rule as the fit — such a path has no residual
+            bool fin = isfinite(s_t) && isfinite(s_t1[0]);
+#pragma unroll
+            for (int q = 0; q < N::IN; ++q) fin = fin && isfinite(x[0][q]);
+            if (!fin) res = __int_as_float(0x7fc00000);
+        }
+        resid[i] = res;
     }
 }
 
@@ -1190,6 +1221,7 @@ static int make_args(const orp_fit_batch* b, FitArgs& a, bool need_target) {
     a.s_t = b->d_s_t; a.s_t1 = b->d_s_t1; a.feat1 = b->d_feat1; a.feat2 = b->d_feat2; a.target = b->d_target;
     a.count = b->count; a.inv_scale = b->inv_scale; a.inv_scale_f = (float)b->inv_scale;
     a.b_t = (float)(b->bond_t * b->inv_scale); a.b_t1 = (float)(b->bond_t1 * b->inv_scale);
+    a.skip = (b->reserved & ORP_FIT_SKIP_NONFINITE) ? 1 : 0;
     return ORP_OK;
 }
 
@@ -1429,6 +1461,7 @@ extern "C" int orp_fit_epoch_minibatch(const orp_fit_batch* b, float* d_params, 
     if (rc) return rc;
     ORP_REQUIRE(d_params && d_state, "null pointer");
     ORP_REQUIRE(batch_size >= 1, "batch_size must be >= 1");
+    ORP_REQUIRE(!a.skip, "ORP_FIT_SKIP_NONFINITE is not available in the Keras-faithful mini-batch driver");
     cudaStream_t st = (cudaStream_t)stream;
 #define CALL_MINI(NET, LOSS, T) fit_minibatch_kernel<NET, LOSS, T><<<1, kMiniThreads, 0, st>>>(a, d_params, d_state, batch_size, epoch_seed)
     ORP_FIT_DISPATCH(CALL_MINI);

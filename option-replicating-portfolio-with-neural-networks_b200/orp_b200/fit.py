@@ -154,11 +154,13 @@ class ReplicationNet:
                 self._equal_counts[count] = int(t[0]) == -int(t[1])
         return self._equal_counts[count]
 
-    def batch(self, s_t, s_t1, target, inv_scale, bond_t, bond_t1, loss="mse", feat1=None, feat2=None):
+    def batch(self, s_t, s_t1, target, inv_scale, bond_t, bond_t1, loss="mse", feat1=None, feat2=None,
+              skip_nonfinite: bool = False):
         torch = _lib.require_cuda()
         b = _lib.FitBatch()
         b.net, b.loss = _lib.NET[self.net], _lib.LOSS[loss]
         b.paths_dtype = _lib.F64 if s_t.dtype == torch.float64 else _lib.F32
+        b.reserved = 1 if skip_nonfinite else 0          # ORP_FIT_SKIP_NONFINITE
         b.count = s_t.numel()
         for t in (s_t, s_t1, target, feat1, feat2):
             if t is not None and not t.is_contiguous():
@@ -295,7 +297,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
                     epochs_first: int = 500, epochs_next: int = 100, patience_first: int = 50, patience_next: int = 7,
                     batch_size: int = 512, shuffle_seed: int = 0, features=None, second_model: bool = False,
                     cost_of_capital: float = 0.1, check_every: int = 16, verbose: bool = False, on_step=None,
-                    steps_per_epoch: int = 8, var_quantiles=None, on_step_end=None):
+                    steps_per_epoch: int = 8, var_quantiles=None, on_step_end=None, skip_nonfinite: bool = False):
     """Backward replication over all kept columns.
 
     ``paths_tm``: TIME-MAJOR ``(n_cols, count)`` CUDA tensor of this rank's paths; ``bond``: ``n_cols`` bond
@@ -311,6 +313,10 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
     ``values[:, t+1] - phi Y_{t+1} - psi B_{t+1}`` over ALL paths of all ranks (``Replicating_Portfolio.py:120-122``),
     by radix select on the device; reported as ``steps[i]["VaR"]``.  ``on_step_end(rec)`` is called with each record.
 
+    ``skip_nonfinite`` (opt-in, not the reference's behaviour): paths whose features, prices or target are NaN / inf
+    take no part in the fits, keep NaN as their value and stay out of the means and quantiles — without it one such
+    path turns every weight into NaN, exactly as in the reference.
+
     Returns ``dict(V0, phi0, psi0, steps=[...], launches)`` in network units."""
     torch = _lib.require_cuda()
     n_cols, count = paths_tm.shape
@@ -318,7 +324,12 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
     bond = np.asarray(bond, dtype=np.float64)
     if bond.shape != (n_cols,):
         raise ValueError("bond must have one entry per kept column")
-    tot = torch.tensor([float(count), float(terminal_values.double().sum())], dtype=torch.float64, device=device)
+    if skip_nonfinite:
+        t_fin = torch.isfinite(terminal_values) & torch.isfinite(paths_tm[-1])     # e.g. -inf price, payoff 0
+        t_sum, t_cnt = terminal_values.double()[t_fin].sum(), int(t_fin.sum())
+    else:
+        t_sum, t_cnt = terminal_values.double().sum(), count
+    tot = torch.tensor([float(t_cnt), float(t_sum)], dtype=torch.float64, device=device)
     allreduce_sum_(tot, group)
     tot = tot.cpu().numpy()
     total = float(tot[0]) if total_paths is None else float(total_paths)
@@ -337,12 +348,17 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
         if on_step is not None:
             on_step({"t_i": t_i})
         f1, f2 = features(t_i) if features is not None else (None, None)
-        common = dict(inv_scale=1.0 / scale, bond_t=bond[t_i], bond_t1=bond[t_i + 1], feat1=f1, feat2=f2)
+        common = dict(inv_scale=1.0 / scale, bond_t=bond[t_i], bond_t1=bond[t_i + 1], feat1=f1, feat2=f2,
+                      skip_nonfinite=skip_nonfinite)
         b = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="mse", **common)
         h = model.fit(b, opt1, epochs_first if first else epochs_next, patience_first if first else patience_next,
                       use_schedule=first, mode=mode, batch_size=batch_size,
                       shuffle_seed=shuffle_seed * 4096 + 2 * t_i, check_every=check_every, steps_per_epoch=steps_per_epoch)
         sums = model.predict(b, v_cur)
+        if skip_nonfinite:                              # the means are over the paths that took part (NaN marks the others)
+            n_ok = torch.isfinite(v_cur).sum().double().reshape(1)
+            allreduce_sum_(n_ok, group)
+            total = max(float(n_ok), 1.0)
         rec = dict(t_i=t_i, epochs_run=h["epochs_run"], loss=h["loss"], stopped_early=h["stopped_early"],
                    mean_V=sums[0] / total, phi=sums[1] / total, psi=sums[2] / total, mae=sums[3] / total)
         if second_model:
@@ -361,7 +377,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
             if resid_buf is None:
                 resid_buf = torch.empty_like(v_next)
             model.residuals(b2 if second_model else b, resid_buf)          # weights as they stand after the step's fits
-            rec["VaR"] = quantiles(resid_buf, var_quantiles, group).tolist()
+            rec["VaR"] = quantiles(resid_buf, var_quantiles, group, ignore_nan=skip_nonfinite).tolist()
         steps.append(rec)
         if on_step_end is not None:
             on_step_end(rec)

@@ -21,8 +21,9 @@ def _key_to_float(key: int) -> float:
     return float(np.array([bits], dtype=np.uint32).view(np.float32)[0])
 
 
-def _kth_key(x, k: int, group):
-    """Order-preserving key of the k-th smallest element (0-based) over all ranks; None when a NaN is present."""
+def _kth_key(x, k: int, group, ignore_nan: bool = False):
+    """Order-preserving key of the k-th smallest element (0-based) over all ranks; None when a NaN is present
+    (unless NaNs are ignored: they are never histogrammed, so they simply do not take part)."""
     torch = _lib.require_cuda()
     L = _lib.lib()
     hist = torch.zeros(BINS, dtype=torch.int64, device=x.device)
@@ -32,7 +33,7 @@ def _kth_key(x, k: int, group):
         _lib.check(L.orp_select_hist(_lib.ptr(x), x.numel(), shift, prefix, mask, _lib.ptr(hist), _lib.stream_ptr()))
         allreduce_sum_(hist, group)
         h = hist.cpu().numpy()
-        if h[256] > 0:
+        if h[256] > 0 and not ignore_nan:
             return None
         cum = np.cumsum(h[:256])
         d = int(np.searchsorted(cum, k, side="right"))
@@ -59,9 +60,10 @@ def _successor(x, key: int, group):
     return int(o[0]), int(o[1])
 
 
-def quantiles(x, qs, group=None) -> np.ndarray:
+def quantiles(x, qs, group=None, ignore_nan: bool = False) -> np.ndarray:
     """``np.quantile(x, qs)`` (linear interpolation) of a contiguous CUDA fp32 vector ``x`` — of the concatenation
-    of every rank's ``x`` when distributed.  Returns float64; NaN if any element is NaN, like NumPy."""
+    of every rank's ``x`` when distributed.  Returns float64; NaN if any element is NaN, like NumPy — or, with
+    ``ignore_nan=True``, ``np.nanquantile``."""
     torch = _lib.require_cuda()
     if x.dtype != torch.float32 or not x.is_contiguous() or x.dim() != 1:
         raise ValueError("x must be a contiguous 1-D float32 CUDA tensor")
@@ -69,6 +71,8 @@ def quantiles(x, qs, group=None) -> np.ndarray:
     if ((qs < 0) | (qs > 1)).any():
         raise ValueError("Quantiles must be in the range [0, 1]")          # numpy's message
     n = torch.tensor([x.numel()], dtype=torch.int64, device=x.device)
+    if ignore_nan:
+        n -= torch.isnan(x).sum()
     allreduce_sum_(n, group)
     n = int(n)
     if n == 0:
@@ -79,7 +83,7 @@ def quantiles(x, qs, group=None) -> np.ndarray:
             h = (n - 1) * q
             k = int(np.floor(h))
             g = h - k
-            key = _kth_key(x, k, group)
+            key = _kth_key(x, k, group, ignore_nan)
             if key is None:
                 out[:] = np.nan
                 break

@@ -212,3 +212,110 @@ def test_backward_replication_multistep_and_second_model(cuda):
                                     epochs_first=60, epochs_next=10)
     assert np.isfinite([res2["V0"], res2["phi0"], res2["psi0"]]).all()
     assert all("loss2" in st and st["epochs_run2"] >= 1 for st in res2["steps"])
+
+
+def _poison(s_t, s_t1, y, f1, f2, net):
+    """Spoil a few samples the ways the arithmetic Euler step does (SURVEY C-1): -inf / NaN prices, NaN targets."""
+    n = s_t.size
+    bad = np.unique(np.concatenate([[0, n - 1], np.random.default_rng(9).choice(n, 9, replace=False)]))
+    s_t, s_t1, y, f1, f2 = (a.copy() for a in (s_t, s_t1, y, f1, f2))
+    for j, i in enumerate(bad):
+        k = j % (5 if net == "rp" else 4)
+        if k == 0: s_t[i] = np.nan
+        elif k == 1: s_t1[i] = -np.inf
+        elif k == 2: y[i] = np.nan
+        elif k == 3: s_t[i], s_t1[i] = -np.inf, np.nan
+        else: f1[i] = np.inf
+    return bad, (s_t, s_t1, y, f1, f2)
+
+
+@pytest.mark.parametrize("net", ["eo", "rp"])
+@pytest.mark.parametrize("loss", ["mse", "pinball"])
+def test_skip_nonfinite_gradient_equals_the_clean_subset(cuda, net, loss):
+    """ORP_FIT_SKIP_NONFINITE (opt-in, no counterpart in the reference): the [gradient, loss, count] vector of a batch
+    with spoiled samples equals the vector of the batch without them (different tile map => summation order differs:
+    2e-6 of the max-norm); without the flag the same batch gives NaN, as in the reference."""
+    from orp_b200 import _lib
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    n = 70_001
+    clean = _toy(n, 4, net)
+    bad, dirty = _poison(*clean, net)
+    keep = np.setdiff1d(np.arange(n), bad)
+    sub = tuple(np.ascontiguousarray(a[keep]) for a in clean)
+    p0 = init_params(net, 7, 0.1 if net == "eo" else [0.9, 0.1])
+    p0 += np.random.default_rng(3).normal(0, 0.2, p0.shape).astype(np.float32)
+    dev = lambda a: torch.from_numpy(a).to(cuda)
+    L = _lib.lib()
+
+    def gsum(data, skip):
+        s_t, s_t1, y, f1, f2 = data
+        model = ReplicationNet(net, p0, cuda)
+        opt = Optimizer(cuda)
+        b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / 100.0, 1.02, 1.03, loss=loss, skip_nonfinite=skip,
+                        feat1=dev(f1) if net == "rp" else None, feat2=dev(f2) if net == "rp" else None)
+        _lib.check(L.orp_fit_begin(_lib.ptr(opt.state), 5, 5, 0, _lib.stream_ptr()))
+        _lib.check(L.orp_fit_grad(C.byref(b), _lib.ptr(model.params), _lib.ptr(opt.state), _lib.ptr(model.gsum),
+                                  _lib.ptr(model.scratch), _lib.stream_ptr()))
+        g = model.gsum.cpu().numpy().copy()
+        vals = torch.empty(s_t.size, dtype=torch.float32, device=cuda)
+        sums = model.predict(b, vals)
+        res = torch.empty_like(vals)
+        model.residuals(b, res)
+        return g, sums, vals.cpu().numpy(), res.cpu().numpy()
+
+    g_skip, s_skip, v_skip, r_skip = gsum(dirty, True)
+    g_sub, s_sub, v_sub, r_sub = gsum(sub, False)
+    g_nan, s_nan, _, _ = gsum(dirty, False)
+    P = _lib.FIT_MAX_PARAMS
+    assert g_skip[P + 1] == n - bad.size == g_sub[P + 1]
+    assert np.isfinite(g_skip[:P + 1]).all()
+    np.testing.assert_allclose(g_skip[:P + 1], g_sub[:P + 1], rtol=0, atol=2e-6 * np.abs(g_sub[:P + 1]).max())
+    assert np.isnan(g_nan[:P + 1]).any() and g_nan[P + 1] == n                  # the reference's behaviour
+    # predict: spoiled paths are marked NaN and left out of the sums; the others are untouched
+    np.testing.assert_allclose(s_skip, s_sub, rtol=1e-9)
+    assert np.isnan(v_skip[bad]).all() and np.array_equal(v_skip[keep], v_sub)
+    assert np.isnan(r_skip[bad]).all() and np.array_equal(r_skip[keep], r_sub)
+    assert not np.isfinite(s_nan).all()
+    with pytest.raises(RuntimeError, match="mini-batch"):
+        model = ReplicationNet(net, p0, cuda)
+        opt = Optimizer(cuda)
+        b = model.batch(dev(dirty[0]), dev(dirty[1]), dev(dirty[2]), 1 / 100.0, 1.02, 1.03, loss=loss, skip_nonfinite=True,
+                        feat1=dev(dirty[3]) if net == "rp" else None, feat2=dev(dirty[4]) if net == "rp" else None)
+        model.fit(b, opt, 1, 1, mode="keras")
+
+
+def test_skip_nonfinite_backward_replication(cuda):
+    """The reference's ARITHMETIC Euler paths with -inf normals (exact-zero Sobol coordinates, here planted): without
+    the flag every result is NaN like the reference's; with it the run equals, to fp32 summation order, the run
+    on the path set without those paths, and the VaR quantiles are those of the remaining residuals."""
+    import orp_b200
+    p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 12)
+    m, D = 14, 6
+    tm = orp_b200.simulate_paths("gbm_euler", p, m=m, steps=D, time_major=True).clone()
+    bad = np.array([0, 77, 5000, 2 ** m - 1])
+    tm[2:, bad[0]] = float("nan")                       # what -inf at step 2 becomes one step later
+    tm[2, bad[0]] = float("-inf")
+    tm[D, bad[1]] = float("-inf")
+    tm[1:, bad[2]] = float("nan")
+    tm[4:, bad[3]] = float("nan")
+    keep = np.setdiff1d(np.arange(2 ** m), bad)
+    tm_sub = tm[:, torch.from_numpy(keep).to(cuda)].contiguous()
+    bond = orp_b200.bond_curve(0.05, D / 12, D + 1)
+
+    def run(paths, **kw):
+        vals = torch.empty(paths.shape[1], dtype=torch.float32, device=cuda)
+        orp_b200.payoff_sums(paths, [100.0], [-1], "call", values_out=vals, value_scale=1 / 100.0)
+        return orp_b200.fit_replication(paths, bond, vals, net="eo", scale=100.0, epochs_first=40, epochs_next=6,
+                                        patience_first=100, patience_next=100, var_quantiles=(.98, .99), **kw)
+
+    ref = run(tm_sub)
+    got = run(tm, skip_nonfinite=True)
+    nan = run(tm)
+    assert np.isnan(nan["V0"]) and np.isnan(nan["phi0"])
+    for k in ("V0", "phi0", "psi0"):
+        assert abs(got[k] - ref[k]) < 2e-3 * max(abs(ref[k]), 1.0), (k, got[k], ref[k])
+    for a, b in zip(got["steps"], ref["steps"]):
+        assert a["epochs_run"] == b["epochs_run"]
+        np.testing.assert_allclose(a["VaR"], b["VaR"], rtol=0, atol=2e-3)
+    v0 = got["values0"].cpu().numpy()
+    assert np.isnan(v0[bad]).all() and np.isfinite(v0[keep]).all()

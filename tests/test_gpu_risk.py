@@ -52,6 +52,20 @@ def test_quantiles_nan_and_errors(cuda):
         orp_b200.quantiles(torch.ones(4, device=cuda, dtype=torch.float64), [0.5])
 
 
+def test_quantiles_ignore_nan_is_nanquantile(cuda):
+    """ignore_nan=True (used by fit_replication(skip_nonfinite=True)): NaN entries take no part, like np.nanquantile."""
+    import orp_b200
+    rng = np.random.default_rng(11)
+    x = (rng.standard_normal(100_003) * 2).astype(np.float32)
+    x[rng.choice(x.size, 37, replace=False)] = np.nan
+    x[:3] = [np.nan, 5.0, np.nan]
+    got = orp_b200.quantiles(torch.from_numpy(x).cuda(), QS, ignore_nan=True)
+    np.testing.assert_allclose(got, np.nanquantile(x.astype(np.float64), QS), rtol=1e-12, atol=0)
+    assert np.isnan(orp_b200.quantiles(torch.from_numpy(x).cuda(), QS)).all()
+    allnan = torch.full((5,), float("nan"), device=cuda)
+    assert np.isnan(orp_b200.quantiles(allnan, [0.5], ignore_nan=True)).all()
+
+
 def test_step_var_quantiles_are_the_quantiles_of_the_residuals(cuda):
     """fit_replication(var_quantiles=...) reports, per time step, np.quantile of  values[:, t+1] - V(X1)  (the
     reference's VaR array) with the weights left by that step's fits."""
