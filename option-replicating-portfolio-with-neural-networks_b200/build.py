@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liborp_b200.so")
 SOURCES = ["orp_sobol_host.cu", "orp_paths.cu", "orp_payoff.cu", "orp_fit.cu", "orp_select.cu", "orp_survivors.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]
+              "-Xcompiler", "-fPIC", "-shared", "-cudart", "static", "--threads", "0"]
 
 
 def nvcc_path() -> str:

@@ -534,13 +534,14 @@ __device__ __forceinline__ void load_raw(const FitArgs& a, uint64_t i, RawSample
     }
 }
 
-template <int NET, typename T>
+template <int NET, typename T, bool SKIP>
 __device__ __forceinline__ bool unpack_raw(const FitArgs& a, const RawSample<NET, T>& r, float (&x)[Net<NET>::IN], float& s_t1, float& y) {
     x[0] = (float)((double)r.s_t * a.inv_scale);          // divide in fp64, then Keras' cast
     s_t1 = (float)((double)r.s_t1 * a.inv_scale);
     y = r.y;
     if (NET == ORP_NET_RP) { x[1] = r.f1; x[Net<NET>::IN - 1] = r.f2; }
-    if (a.skip) {                                          // opt-in: a non-finite sample is replaced by zeros and reported
+    if (SKIP) {                                            // opt-in (own instantiation: the default loop carries none of it):
+                                                           // a non-finite sample is replaced by zeros and reported
         bool fin = isfinite(s_t1) && isfinite(y);
 #pragma unroll
         for (int q = 0; q < Net<NET>::IN; ++q) fin = fin && isfinite(x[q]);
@@ -577,7 +578,7 @@ __device__ __forceinline__ void load_first_tile(const FitArgs& a, uint32_t block
 
 // Forward + backward over this block's tiles of one batch: block `block` of `n_blocks` takes tiles block,
 // block + n_blocks, ...  `cur` holds the first tile (load_first_tile).  Adds into g / loss / n.
-template <int NET, int LOSS, typename T>
+template <int NET, int LOSS, typename T, bool SKIP>
 __device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa, uint32_t block, uint32_t n_blocks,
                                                  RawSample<NET, T> (&cur)[kFitUnroll<NET>], Grads<NET>& g, float& loss, uint32_t& n) {
     using N = Net<NET>;
@@ -600,7 +601,7 @@ __device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa
                 bool fin[S];
                 Acts<NET, S> act;
 #pragma unroll
-                for (int s = 0; s < S; ++s) fin[s] = unpack_raw<NET, T>(a, cur[u + s], x[s], s_t1[s], y[s]);     // out-of-range slots hold zeros
+                for (int s = 0; s < S; ++s) fin[s] = unpack_raw<NET, T, SKIP>(a, cur[u + s], x[s], s_t1[s], y[s]);     // out-of-range slots hold zeros
                 net_forward<NET, S>(s_wa, x, s_t1, a.b_t1, act, phi, psi, v);
 #pragma unroll
                 for (int s = 0; s < S; ++s) {
@@ -621,7 +622,7 @@ __device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa
 
 // STEP = true: the whole optimiser step in this one launch — the block that arrives last (a ticket counter in
 // the state block) adds the partials in the same fixed order as fit_reduce_kernel and applies the update.
-template <int NET, int LOSS, typename T, bool STEP>
+template <int NET, int LOSS, typename T, bool STEP, bool SKIP>
 __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, float* params, double* state,
                                                                double* __restrict__ partials, double* __restrict__ gsum, int flags) {
     using N = Net<NET>;
@@ -637,7 +638,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
     uint32_t n = 0;
     RawSample<NET, T> first[kFitUnroll<NET>];
     load_first_tile<NET, T>(a, blockIdx.x, first);
-    accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, gridDim.x, first, g, loss, n);
+    accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, blockIdx.x, gridDim.x, first, g, loss, n);
     block_reduce_to<NET>(g, loss, n, partials + (size_t)blockIdx.x * kGsum);
     if (STEP) {
         __shared__ bool s_last;
@@ -764,7 +765,7 @@ __device__ __forceinline__ FitArgs part_args(const RunArgs& r, int k, uint32_t G
     return a;
 }
 
-template <int NET, int LOSS, typename T>
+template <int NET, int LOSS, typename T, bool SKIP>
 __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, float* params, double* state,
                                                               double* __restrict__ partials, double* __restrict__ gsum) {
     using N = Net<NET>;
@@ -818,7 +819,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             g.zero();
             float loss = 0.f;
             uint32_t n = 0;
-            if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T>(a, s_wa, blockIdx.x, g_k, first, g, loss, n);
+            if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, blockIdx.x, g_k, first, g, loss, n);
             ORP_TRACE(1);
 
             // ---- block total -> tagged entry [parity][column][block] (blocks without tiles in this batch publish nothing)
@@ -1256,9 +1257,11 @@ extern "C" int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const
     cudaStream_t st = (cudaStream_t)stream;
     const int grid = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
     double* partials = reinterpret_cast<double*>(d_scratch);
-#define CALL_GRAD(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, false><<<grid, kFitThreads, 0, st>>>(a, const_cast<float*>(d_params), const_cast<double*>(d_state), partials, d_gsum, 0)
-    ORP_FIT_DISPATCH(CALL_GRAD);
+#define CALL_GRAD(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, false, false><<<grid, kFitThreads, 0, st>>>(a, const_cast<float*>(d_params), const_cast<double*>(d_state), partials, d_gsum, 0)
+#define CALL_GRAD_SKIP(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, false, true><<<grid, kFitThreads, 0, st>>>(a, const_cast<float*>(d_params), const_cast<double*>(d_state), partials, d_gsum, 0)
+    if (a.skip) ORP_FIT_DISPATCH(CALL_GRAD_SKIP); else ORP_FIT_DISPATCH(CALL_GRAD);
 #undef CALL_GRAD
+#undef CALL_GRAD_SKIP
     ORP_LAUNCH_CHECK("fit_grad_kernel");
     fit_reduce_kernel<<<1, 256, 0, st>>>(partials, grid, d_state, d_gsum);
     ORP_LAUNCH_CHECK("fit_reduce_kernel");
@@ -1272,9 +1275,11 @@ static int fit_step_launch(const orp_fit_batch* b, float* d_params, double* d_st
     if (rc) return rc;
     const int grid = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
     double* partials = reinterpret_cast<double*>(d_scratch);
-#define CALL_STEP(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, true><<<grid, kFitThreads, 0, st>>>(a, d_params, d_state, partials, d_gsum, flags)
-    ORP_FIT_DISPATCH(CALL_STEP);
+#define CALL_STEP(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, true, false><<<grid, kFitThreads, 0, st>>>(a, d_params, d_state, partials, d_gsum, flags)
+#define CALL_STEP_SKIP(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, true, true><<<grid, kFitThreads, 0, st>>>(a, d_params, d_state, partials, d_gsum, flags)
+    if (a.skip) ORP_FIT_DISPATCH(CALL_STEP_SKIP); else ORP_FIT_DISPATCH(CALL_STEP);
 #undef CALL_STEP
+#undef CALL_STEP_SKIP
     ORP_LAUNCH_CHECK("fit_grad_kernel (single-launch step)");
     return ORP_OK;
 }
@@ -1319,9 +1324,11 @@ static int fit_run_launch(const orp_fit_batch* b, int n_parts, float* d_params, 
     double* partials = reinterpret_cast<double*>(d_scratch);
     void* args[] = {(void*)&r, (void*)&d_params, (void*)&d_state, (void*)&partials, (void*)&d_gsum};
     const void* fn = nullptr;
-#define PICK_RUN(NET, LOSS, T) fn = (const void*)fit_run_kernel<NET, LOSS, T>
-    ORP_FIT_DISPATCH(PICK_RUN);
+#define PICK_RUN(NET, LOSS, T) fn = (const void*)fit_run_kernel<NET, LOSS, T, false>
+#define PICK_RUN_SKIP(NET, LOSS, T) fn = (const void*)fit_run_kernel<NET, LOSS, T, true>
+    if (r.a.skip) ORP_FIT_DISPATCH(PICK_RUN_SKIP); else ORP_FIT_DISPATCH(PICK_RUN);
 #undef PICK_RUN
+#undef PICK_RUN_SKIP
     ORP_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kFitThreads), args, 0, st));
     return ORP_OK;
 }

@@ -281,7 +281,7 @@ def test_skip_nonfinite_gradient_equals_the_clean_subset(cuda, net, loss):
         opt = Optimizer(cuda)
         b = model.batch(dev(dirty[0]), dev(dirty[1]), dev(dirty[2]), 1 / 100.0, 1.02, 1.03, loss=loss, skip_nonfinite=True,
                         feat1=dev(dirty[3]) if net == "rp" else None, feat2=dev(dirty[4]) if net == "rp" else None)
-        model.fit(b, opt, 1, 1, mode="keras")
+        model.fit(b, opt, 1, 1, False, mode="keras")
 
 
 def test_skip_nonfinite_backward_replication(cuda):
