@@ -276,7 +276,7 @@ def test_skip_nonfinite_gradient_equals_the_clean_subset(cuda, net, loss):
     assert np.isnan(v_skip[bad]).all() and np.array_equal(v_skip[keep], v_sub)
     assert np.isnan(r_skip[bad]).all() and np.array_equal(r_skip[keep], r_sub)
     assert not np.isfinite(s_nan).all()
-    with pytest.raises(RuntimeError, match="mini-batch"):
+    with pytest.raises(ValueError, match="mini-batch"):
         model = ReplicationNet(net, p0, cuda)
         opt = Optimizer(cuda)
         b = model.batch(dev(dirty[0]), dev(dirty[1]), dev(dirty[2]), 1 / 100.0, 1.02, 1.03, loss=loss, skip_nonfinite=True,
