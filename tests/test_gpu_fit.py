@@ -67,6 +67,51 @@ def test_gradient_and_loss_match_autograd(cuda, net, loss, n):
     assert np.abs(g[:P] / n - ref).max() <= 2e-4 * max(np.abs(ref).max(), 1e-6)
 
 
+@pytest.mark.parametrize("net", ["eo", "rp"])
+def test_fp32_path_arrays_give_the_gradient_of_the_rounded_prices(cuda, net):
+    """orp_fit_batch.paths_dtype = ORP_F32 (paths stored in fp32, the north_star's 1e-4 mode): same kernels, float
+    loads.  The [gradient, loss, count] vector must be that of the fp32-rounded prices (autograd, 2e-4 of the
+    max-norm) and the persistent driver must agree bit for bit with the two-stage one on it."""
+    from orp_b200 import _lib
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    n = 33_333
+    s_t, s_t1, y, f1, f2 = _toy(n, 5, net)
+    s_t, s_t1 = s_t.astype(np.float32), s_t1.astype(np.float32)
+    scale, b_t, b_t1 = 100.0, 1.02, 1.03
+    p0 = init_params(net, 7, 0.1 if net == "eo" else [0.9, 0.1])
+    p0 += np.random.default_rng(3).normal(0, 0.2, p0.shape).astype(np.float32)
+    dev = lambda a: torch.from_numpy(a).to(cuda)
+    feats = dict(feat1=dev(f1), feat2=dev(f2)) if net == "rp" else {}
+    model = ReplicationNet(net, p0, cuda)
+    opt = Optimizer(cuda)
+    b = model.batch(dev(s_t), dev(s_t1), dev(y), 1 / scale, b_t, b_t1, loss="mse", **feats)
+    assert b.paths_dtype == _lib.F32
+    L = _lib.lib()
+    _lib.check(L.orp_fit_begin(_lib.ptr(opt.state), 5, 5, 0, _lib.stream_ptr()))
+    _lib.check(L.orp_fit_grad(C.byref(b), _lib.ptr(model.params), _lib.ptr(opt.state), _lib.ptr(model.gsum),
+                              _lib.ptr(model.scratch), _lib.stream_ptr()))
+    g = model.gsum.cpu().numpy()
+    x, _, p1, yt = _oracle_inputs(net, s_t.astype(np.float64), s_t1.astype(np.float64), y, f1, f2, scale, b_t, b_t1)
+    w = torch.from_numpy(p0.copy()).double().requires_grad_(True)
+    v, _, _ = ofit.forward(w, net, x.double(), p1.double())
+    l = ofit.loss_fn("mse", yt.double(), v)
+    (gr,) = torch.autograd.grad(l, w)
+    ref = gr.numpy()
+    assert g[_lib.FIT_MAX_PARAMS + 1] == n
+    np.testing.assert_allclose(g[_lib.FIT_MAX_PARAMS] / n, float(l.detach()), rtol=2e-5, atol=1e-9)
+    assert np.abs(g[:model.P] / n - ref).max() <= 2e-4 * max(np.abs(ref).max(), 1e-6)
+    # three epochs through the persistent kernel and through the two-stage driver: identical weights
+    outs = []
+    for two_stage in (False, True):
+        mdl = ReplicationNet(net, p0, cuda)
+        o = Optimizer(cuda)
+        bb = mdl.batch(dev(s_t), dev(s_t1), dev(y), 1 / scale, b_t, b_t1, loss="mse", **feats)
+        mdl.two_stage = two_stage
+        mdl.fit(bb, o, 3, 3, False, mode="scaled", steps_per_epoch=2)
+        outs.append(mdl.params[:mdl.P].cpu().numpy().copy())
+    assert np.array_equal(outs[0], outs[1])
+
+
 @pytest.mark.parametrize("spe", [1, 8])
 @pytest.mark.parametrize("net", ["eo", "rp"])
 def test_scaled_fit_tracks_oracle(cuda, net, spe):
