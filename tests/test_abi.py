@@ -38,7 +38,8 @@ def test_struct_layouts_match_header():
     assert _lib.lib().orp_version() >= 100
 
 
-@pytest.mark.parametrize("d,seed", [(1, 7), (2, 1235), (53, 1235), (253, 1234), (253, 1235), (366, 1235)])
+@pytest.mark.parametrize("d,seed", [(1, 7), (2, 1235), (53, 1235), (253, 1234), (253, 1235), (366, 1235),
+                                    (3651, 1235), (21201, 3)])          # RP.py at T = 10, dt = 1/365; SciPy's maximum
 def test_host_setup_bit_exact(d, seed):
     from orp_b200.sobol import SobolEngine
     e = SobolEngine(d, seed)
