@@ -534,6 +534,18 @@ __device__ __forceinline__ void load_raw(const FitArgs& a, uint64_t i, RawSample
     }
 }
 
+// the same for the passes that may run without a target (predict)
+template <int NET, typename T>
+__device__ __forceinline__ void load_raw_any(const FitArgs& a, uint64_t i, RawSample<NET, T>& r) {
+    r.s_t = reinterpret_cast<const T*>(a.s_t)[i];
+    r.s_t1 = reinterpret_cast<const T*>(a.s_t1)[i];
+    r.y = a.target ? a.target[i] : 0.f;
+    if (NET == ORP_NET_RP) {
+        r.f1 = a.feat1 ? a.feat1[i] : 1.f;
+        r.f2 = a.feat2 ? a.feat2[i] : 0.f;
+    }
+}
+
 template <int NET, typename T, bool SKIP>
 __device__ __forceinline__ bool unpack_raw(const FitArgs& a, const RawSample<NET, T>& r, float (&x)[Net<NET>::IN], float& s_t1, float& y) {
     x[0] = (float)((double)r.s_t * a.inv_scale);          // divide in fp64, then Keras' cast
@@ -1014,39 +1026,35 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitAr
     __syncthreads();
     const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
     double sv = 0.0, sphi = 0.0, spsi = 0.0, sae = 0.0;
-    constexpr int S = 1;                                   // memory-bound: occupancy (64 registers) beats weight reuse here
+    // One sample per thread and iteration (memory-bound: occupancy at 64 registers beats weight reuse here); the
+    // loads of the thread's NEXT sample are issued before the arithmetic of the current one, which doubles the bytes
+    // in flight per SM (32 warps x 20 B x 32 lanes alone do not cover the HBM latency-bandwidth product).
     const uint64_t stride = (uint64_t)gridDim.x * kFitThreads;
-    for (uint64_t i = (uint64_t)blockIdx.x * kFitThreads + threadIdx.x; i < a.count; i += S * stride) {
-        float x[S][N::IN], s_t[S], s_t1[S], phi[S], psi[S], v0[S];
-        Acts<NET, S> act;
+    uint64_t i = (uint64_t)blockIdx.x * kFitThreads + threadIdx.x;
+    RawSample<NET, T> nxt;
+    nxt.s_t = nxt.s_t1 = T(0); nxt.y = nxt.f1 = nxt.f2 = 0.f;
+    if (i < a.count) load_raw_any<NET, T>(a, i, nxt);
+    for (; i < a.count; i += stride) {
+        const RawSample<NET, T> cur = nxt;
+        if (i + stride < a.count) load_raw_any<NET, T>(a, i + stride, nxt);
+        float x[1][N::IN], s_t[1], s_t1[1], phi[1], psi[1], v0[1], tgt;
+        Acts<NET, 1> act;
+        unpack_raw<NET, T, false>(a, cur, x[0], s_t1[0], tgt);
+        s_t[0] = x[0][0];
+        net_forward<NET, 1>(s_wa, x, s_t, a.b_t, act, phi, psi, v0);          // model.predict(X0): prices at t
+        const float v1 = fmaf(phi[0], s_t1[0], psi[0] * a.b_t1);              // model.predict(X1): prices at t+1
+        if (a.skip) {                                      // opt-in: a path with a non-finite feature, price or target
+            bool fin = isfinite(s_t1[0]) && isfinite(tgt); // stays marked (NaN) and out of the sums
 #pragma unroll
-        for (int s = 0; s < S; ++s) {
-            const uint64_t is = i + s * stride;
-#pragma unroll
-            for (int q = 0; q < N::IN; ++q) x[s][q] = 0.f;
-            s_t[s] = s_t1[s] = 0.f;
-            if (is < a.count) load_sample<NET, T>(a, is, x[s], s_t[s], s_t1[s]);
-        }
-        net_forward<NET, S>(s_wa, x, s_t, a.b_t, act, phi, psi, v0);          // model.predict(X0): prices at t
-#pragma unroll
-        for (int s = 0; s < S; ++s) {
-            const uint64_t is = i + s * stride;
-            if (is < a.count) {
-                const float v1 = fmaf(phi[s], s_t1[s], psi[s] * a.b_t1);      // model.predict(X1): prices at t+1
-                const float tgt = a.target ? a.target[is] : 0.f;
-                bool fin = isfinite(s_t[s]) && isfinite(s_t1[s]) && isfinite(tgt);
-#pragma unroll
-                for (int q = 0; q < N::IN; ++q) fin = fin && isfinite(x[s][q]);
-                if (a.skip && !fin) {
-                    // opt-in: a path with a non-finite feature, price or target stays marked (NaN) and out of the sums
-                    if (values_out) values_out[is] = __int_as_float(0x7fc00000);
-                    continue;
-                }
-                if (values_out) values_out[is] = v0[s];
-                sv += v0[s]; sphi += phi[s]; spsi += psi[s];
-                if (a.target) sae += fabsf(tgt - v1);                         // 'mae' metric of model.evaluate(X1, ...)
+            for (int q = 0; q < N::IN; ++q) fin = fin && isfinite(x[0][q]);
+            if (!fin) {
+                if (values_out) values_out[i] = __int_as_float(0x7fc00000);
+                continue;
             }
         }
+        if (values_out) values_out[i] = v0[0];
+        sv += v0[0]; sphi += phi[0]; spsi += psi[0];
+        if (a.target) sae += fabsf(tgt - v1);                                 // 'mae' metric of model.evaluate(X1, ...)
     }
     __shared__ double s_red[kFitThreads / 32][4];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1423,7 +1431,10 @@ extern "C" int orp_fit_predict(const orp_fit_batch* b, const float* d_params, fl
     ORP_REQUIRE(d_params && d_sums && d_scratch, "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     uint64_t want = (a.count + kFitThreads - 1) / kFitThreads;
-    const uint64_t cap = (uint64_t)(4 * sm_count() < 512 ? 4 * sm_count() : 512);
+    // four resident blocks per SM (launch bounds), a whole number of waves: 592 blocks on B200, not 512 (3.46 per SM);
+    // their 4 partial sums each fit the 512 x kGsumLen doubles in front of the scratch header many times over
+    uint64_t cap = 4ull * (uint64_t)sm_count();
+    if (cap * 4 > kScrHeader) cap = kScrHeader / 4;
     const int grid = (int)(want < cap ? want : cap);
     double* partials = reinterpret_cast<double*>(d_scratch);
     const bool f64 = b->paths_dtype == ORP_F64;
@@ -1447,7 +1458,7 @@ extern "C" int orp_fit_residuals(const orp_fit_batch* b, const float* d_params, 
     ORP_REQUIRE(d_params && d_resid_out, "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
     uint64_t want = (a.count + kFitThreads - 1) / kFitThreads;
-    const uint64_t cap = (uint64_t)(4 * sm_count() < 512 ? 4 * sm_count() : 512);
+    const uint64_t cap = 4ull * (uint64_t)sm_count();          // four resident blocks per SM, whole waves
     const int grid = (int)(want < cap ? want : cap);
     const bool f64 = b->paths_dtype == ORP_F64;
     if (b->net == ORP_NET_EO) {
