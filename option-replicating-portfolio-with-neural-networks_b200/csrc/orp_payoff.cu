@@ -30,56 +30,92 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-template <typename T>
-__global__ void __launch_bounds__(kPayThreads) payoff_partial_kernel(const PayoffArgs a) {
+// Per-thread accumulators of one chunk of options.  The out-of-the-money tallies are integers (a thread sees far
+// fewer than 2^32 paths) and a NaN price is remembered as a flag instead of being added: per (path, option) the fp64
+// pipe then runs three instructions for a call / put (subtract, compare, add) and two for the floor.
+struct PayAcc {
+    double sum[kPayChunk];
+    unsigned otm[kPayChunk], nan[kPayChunk];
+};
+
+// UU paths of one thread (all of them inside the path range) against the chunk's options.  KIND is a template
+// parameter: the payoff formula is fixed per launch, the option loop carries no dispatch.
+template <typename T, int KIND, int UU>
+__device__ __forceinline__ void payoff_paths(const PayoffArgs& a, const T* __restrict__ paths, uint64_t i, uint64_t stride,
+                                             int o_first, int n_here, bool write_values, PayAcc& acc) {
+    int last_col = -1;
+    double s[UU];
+    unsigned below[UU], any_nan = 0u;
+#pragma unroll
+    for (int u = 0; u < UU; ++u) { s[u] = 0.0; below[u] = 0u; }
+#pragma unroll
+    for (int k = 0; k < kPayChunk; ++k) {
+        if (k < n_here) {                                   // uniform over the grid's y slice
+            const int col = a.cols[o_first + k];
+            if (col != last_col) {                          // options of a sweep arrive grouped by maturity column
+                any_nan = 0u;
+#pragma unroll
+                for (int u = 0; u < UU; ++u) s[u] = (double)paths[(size_t)col * a.ld + i + u * stride];
+#pragma unroll
+                for (int u = 0; u < UU; ++u) {
+                    if (KIND == ORP_PAYOFF_FLOOR) below[u] = s[u] < a.s0 ? 1u : 0u;                // RP.py:89
+                    else any_nan |= s[u] != s[u] ? 1u : 0u;
+                }
+                last_col = col;
+            }
+            const double K = a.strikes[o_first + k];
+#pragma unroll
+            for (int u = 0; u < UU; ++u) {
+                double pay;
+                if (KIND == ORP_PAYOFF_FLOOR) {
+                    pay = s[u] > K ? s[u] : K;                                                     // RP.py:88 (np.where: NaN -> K)
+                    acc.otm[k] += below[u];
+                } else {
+                    const double d = KIND == ORP_PAYOFF_CALL ? s[u] - K : K - s[u];                // EO cell 8
+                    const bool in = d > 0.0;                                                       // false for NaN
+                    pay = in ? d : 0.0;
+                    acc.otm[k] += in ? 0u : 1u;
+                }
+                acc.sum[k] += pay;
+                if (k == 0 && write_values) {
+                    // np.maximum propagates NaN (the sums get it through the flag below)
+                    const double v = (KIND != ORP_PAYOFF_FLOOR && s[u] != s[u]) ? s[u] : pay;
+                    a.values_out[i + u * stride] = (float)(v * a.value_scale);
+                }
+            }
+            if (KIND != ORP_PAYOFF_FLOOR) acc.nan[k] |= any_nan;
+        }
+    }
+}
+
+template <typename T, int KIND>
+__global__ void __launch_bounds__(kPayThreads, 4) payoff_partial_kernel(const PayoffArgs a) {
     const int chunk = blockIdx.y;
     const int o_first = chunk * kPayChunk;
     const int n_here = min(kPayChunk, a.n_opt - o_first);
     const T* __restrict__ paths = reinterpret_cast<const T*>(a.paths);
+    const bool write_values = chunk == 0 && a.values_out != nullptr;
+
+    PayAcc acc;
+#pragma unroll
+    for (int k = 0; k < kPayChunk; ++k) { acc.sum[k] = 0.0; acc.otm[k] = acc.nan[k] = 0u; }
+
+    // four paths per thread and iteration: their column loads are independent, so four 8-byte requests per thread are
+    // in flight (one per thread covered a quarter of the bandwidth-delay product of HBM); the ragged end of the range
+    // goes through the same code one path at a time, so the main loop has no range checks
+    constexpr int U = 4;
+    const uint64_t stride = (uint64_t)gridDim.x * kPayThreads;
+    uint64_t i = (uint64_t)blockIdx.x * kPayThreads + threadIdx.x;
+    for (; i + (U - 1) * stride < a.count; i += U * stride)
+        payoff_paths<T, KIND, U>(a, paths, i, stride, o_first, n_here, write_values, acc);
+    for (; i < a.count; i += stride)
+        payoff_paths<T, KIND, 1>(a, paths, i, stride, o_first, n_here, write_values, acc);
 
     double sum[kPayChunk], otm[kPayChunk];
 #pragma unroll
-    for (int k = 0; k < kPayChunk; ++k) sum[k] = otm[k] = 0.0;
-
-    // four paths per thread and iteration: their column loads are independent, so four 8-byte requests per thread are
-    // in flight (one per thread covered a quarter of the bandwidth-delay product of HBM)
-    constexpr int U = 4;
-    const uint64_t stride = (uint64_t)gridDim.x * kPayThreads;
-    for (uint64_t i = (uint64_t)blockIdx.x * kPayThreads + threadIdx.x; i < a.count; i += U * stride) {
-        int last_col = -1;
-        double s[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) s[u] = 0.0;
-#pragma unroll
-        for (int k = 0; k < kPayChunk; ++k) {
-            if (k < n_here) {
-                const int col = a.cols[o_first + k];
-                if (col != last_col) {
-#pragma unroll
-                    for (int u = 0; u < U; ++u) {
-                        const uint64_t iu = i + u * stride;
-                        s[u] = iu < a.count ? (double)paths[(size_t)col * a.ld + iu] : 0.0;
-                    }
-                    last_col = col;
-                }
-                const double K = a.strikes[o_first + k];
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const uint64_t iu = i + u * stride;
-                    if (iu < a.count) {
-                        double pay, is_otm;
-                        if (a.kind == ORP_PAYOFF_CALL)      { pay = fmax(s[u] - K, 0.0); is_otm = pay > 0.0 ? 0.0 : 1.0; }   // EO cell 8
-                        else if (a.kind == ORP_PAYOFF_PUT)  { pay = fmax(K - s[u], 0.0); is_otm = pay > 0.0 ? 0.0 : 1.0; }
-                        else                                { pay = s[u] > K ? s[u] : K; is_otm = s[u] < a.s0 ? 1.0 : 0.0; } // RP.py:88-89
-                        // np.maximum propagates NaN, fmax does not
-                        if (a.kind != ORP_PAYOFF_FLOOR && s[u] != s[u]) pay = s[u];
-                        sum[k] += pay;
-                        otm[k] += is_otm;
-                        if (k == 0 && chunk == 0 && a.values_out) a.values_out[iu] = (float)(pay * a.value_scale);
-                    }
-                }
-            }
-        }
+    for (int k = 0; k < kPayChunk; ++k) {
+        sum[k] = acc.nan[k] ? __longlong_as_double(0x7ff8000000000000ll) : acc.sum[k];
+        otm[k] = (double)acc.otm[k];
     }
 
     __shared__ double s_red[kPayThreads / 32][2 * kPayChunk];
@@ -97,19 +133,38 @@ __global__ void __launch_bounds__(kPayThreads) payoff_partial_kernel(const Payof
     }
 }
 
-__global__ void payoff_final_kernel(const double* __restrict__ partials, int n_blocks, int n_opt,
-                                    double* __restrict__ sums, double* __restrict__ otm) {
-    const int o = blockIdx.x * blockDim.x + threadIdx.x;       // one thread per (option, quantity)
-    if (o >= 2 * n_opt) return;
+// Second pass: one WARP per (option, quantity).  Lane l adds the partials of blocks l, l + 32, ... in increasing order,
+// then a shuffle tree: a fixed order (the same bits on every launch) with ~n_blocks / 32 dependent additions per lane
+// instead of one thread walking all n_blocks partials (57 us of a 64-option sweep under ncu).
+constexpr int kFinalThreads = 128;
+__global__ void __launch_bounds__(kFinalThreads) payoff_final_kernel(const double* __restrict__ partials, int n_blocks, int n_opt,
+                                                                     double* __restrict__ sums, double* __restrict__ otm) {
+    const int o = (blockIdx.x * kFinalThreads + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (o >= 2 * n_opt) return;                                 // whole warps leave together
     const int opt = o >> 1, which = o & 1;
     const int chunk = opt / kPayChunk, k = opt % kPayChunk;
     double t = 0.0;
-    for (int b = 0; b < n_blocks; ++b)
+    for (int b = lane; b < n_blocks; b += 32)
         t += partials[((size_t)chunk * n_blocks + b) * (2 * kPayChunk) + 2 * k + which];
-    (which ? otm : sums)[opt] = t;
+    t = warp_sum(t);
+    if (lane == 0) (which ? otm : sums)[opt] = t;
 }
 
-static int payoff_blocks() { return 4 * sm_count(); }
+static int payoff_blocks() { return 4 * sm_count(); }        // four resident blocks per SM (launch bounds): whole waves
+
+static void launch_payoff_partial(int dtype, int kind, dim3 grid, cudaStream_t st, const PayoffArgs& a) {
+#define ORP_PAY(T, KIND) payoff_partial_kernel<T, KIND><<<grid, kPayThreads, 0, st>>>(a)
+    if (dtype == ORP_F64) {
+        if (kind == ORP_PAYOFF_CALL) ORP_PAY(double, ORP_PAYOFF_CALL);
+        else if (kind == ORP_PAYOFF_PUT) ORP_PAY(double, ORP_PAYOFF_PUT);
+        else ORP_PAY(double, ORP_PAYOFF_FLOOR);
+    } else {
+        if (kind == ORP_PAYOFF_CALL) ORP_PAY(float, ORP_PAYOFF_CALL);
+        else if (kind == ORP_PAYOFF_PUT) ORP_PAY(float, ORP_PAYOFF_PUT);
+        else ORP_PAY(float, ORP_PAYOFF_FLOOR);
+    }
+#undef ORP_PAY
+}
 
 }  // namespace orp
 
@@ -148,10 +203,9 @@ extern "C" int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, ui
     if ((uint64_t)gx > want) gx = (int)want;
     cudaStream_t st = (cudaStream_t)stream;
     dim3 grid(gx, chunks);
-    if (dtype == ORP_F64) payoff_partial_kernel<double><<<grid, kPayThreads, 0, st>>>(a);
-    else                  payoff_partial_kernel<float><<<grid, kPayThreads, 0, st>>>(a);
+    launch_payoff_partial(dtype, kind, grid, st, a);
     ORP_LAUNCH_CHECK("payoff_partial_kernel");
-    payoff_final_kernel<<<(2 * n_opt + 127) / 128, 128, 0, st>>>(a.partials, gx, n_opt, d_sums, d_otm);
+    payoff_final_kernel<<<(2 * n_opt * 32 + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, st>>>(a.partials, gx, n_opt, d_sums, d_otm);
     ORP_LAUNCH_CHECK("payoff_final_kernel");
     return ORP_OK;
 }
@@ -223,10 +277,9 @@ extern "C" int orp_payoff_reduce_noalloc(const void* d_paths, int dtype, uint64_
     // Nothing in the array has to start at zero: every block of this launch overwrites its own 16 slots and the
     // second kernel reads exactly those gx blocks, so what an earlier call left behind is never looked at.
     dim3 grid(gx, 1);
-    if (dtype == ORP_F64) payoff_partial_kernel<double><<<grid, kPayThreads, 0, st>>>(a);
-    else                  payoff_partial_kernel<float><<<grid, kPayThreads, 0, st>>>(a);
+    launch_payoff_partial(dtype, kind, grid, st, a);
     ORP_LAUNCH_CHECK("payoff_partial_kernel (noalloc)");
-    payoff_final_kernel<<<(2 * n_opt + 127) / 128, 128, 0, st>>>(partials, gx, n_opt, d_sums, d_otm);
+    payoff_final_kernel<<<(2 * n_opt * 32 + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, st>>>(partials, gx, n_opt, d_sums, d_otm);
     ORP_LAUNCH_CHECK("payoff_final_kernel (noalloc)");
     return ORP_OK;
 }
