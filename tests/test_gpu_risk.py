@@ -3,8 +3,6 @@
 
 Order statistics are selected exactly (integer keys), the interpolation is NumPy's ``_lerp`` in fp64: results must
 agree to 1e-12 relative with ``np.quantile`` of the same fp32 values promoted to fp64."""
-import ctypes as C
-
 import numpy as np
 import pytest
 import torch
@@ -70,7 +68,7 @@ def test_step_var_quantiles_are_the_quantiles_of_the_residuals(cuda):
     """fit_replication(var_quantiles=...) reports, per time step, np.quantile of  values[:, t+1] - V(X1)  (the
     reference's VaR array) with the weights left by that step's fits."""
     import orp_b200
-    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    from orp_b200.fit import ReplicationNet
     p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 4)
     tm = orp_b200.simulate_paths("gbm_log", p, m=13, steps=4, device=cuda, time_major=True)
     vals = torch.empty(2 ** 13, dtype=torch.float32, device=cuda)

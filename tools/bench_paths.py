@@ -2,7 +2,6 @@
 """Kernel-level timing of the path kernels (CUDA events, inputs far larger than L2): GB/s of kept columns."""
 import os
 import sys
-import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "option-replicating-portfolio-with-neural-networks_b200")]

@@ -5,7 +5,6 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "option-replicating-portfolio-with-neural-networks_b200")]
-import numpy as np  # noqa: E402
 import torch  # noqa: E402
 import orp_b200  # noqa: E402
 from orp_b200.fit import ReplicationNet, Optimizer, init_params  # noqa: E402
