@@ -199,6 +199,45 @@ def golden_sobol():
     np.savez_compressed(os.path.join(OUT, "sobol_points.npz"), **out)
 
 
+def notebook_fit_log():
+    """What the reference's own Keras run of ``European Options.ipynb`` left in the saved notebook: the training log
+    of cell 13 (52 ``model1.fit`` calls on 4096 paths, batch 512) and the prints of cells 18 and 20.  TensorFlow is
+    not installed, so these stored outputs are the only evidence of the reference's fit; the fit tests hold the
+    oracle and the CUDA path against them statistically (``tests/test_oracle_fit.py``, ``tests/test_gpu_fit.py``)."""
+    import re
+    with open(os.path.join(REF, "European Options.ipynb")) as f:
+        cells = json.load(f)["cells"]
+
+    def text(i):
+        return "".join("".join(o.get("text", [])) for o in cells[i].get("outputs", []) if "text" in o)
+
+    log = text(13)
+    ep = re.findall(r"Epoch (\d+)/(\d+)", log)
+    starts = [i for i, (a, _) in enumerate(ep) if a == "1"]
+    runs = [int(ep[(starts[k + 1] - 1) if k + 1 < len(starts) else -1][0]) for k in range(len(starts))]
+    # the last progress line of every epoch carries that epoch's mean loss
+    per_epoch = re.findall(r"8/8 \[=+\] - [^\n]*? loss: ([0-9.e+-]+) - mae: ([0-9.e+-]+)", log)
+    var = [[float(a), float(b)] for a, b in re.findall(r"VaR: ([0-9.]+) \(98%\),\s+([0-9.]+) \(99%\)", log)]
+    out18, out20 = text(18), text(20)
+    # every fit is followed by one model.evaluate line in the same format: epochs + 1 entries per fit
+    idx, fit_last_loss, eval_loss = 0, [], []
+    for n in runs:
+        fit_last_loss.append(float(per_epoch[idx + n - 1][0]))
+        eval_loss.append(float(per_epoch[idx + n][0]))
+        idx += n + 1
+    assert idx == len(per_epoch), (idx, len(per_epoch))
+    return {
+        "paths": 4096, "columns": 53, "params": {"S0": 100, "K": 100, "r": 0.08, "sigma": 0.15, "T": 1.0, "dt": "1/365",
+                                                "rebalancing": "1/52"},
+        "epochs_per_fit": runs, "fit_last_epoch_loss": fit_last_loss, "evaluate_loss": eval_loss, "VaR_98_99": var,
+        "phi0": float(re.search(r"Phi t=0 : ([0-9.]+)", out18).group(1)),
+        "psi0": float(re.search(r"Psi t=0 : ([0-9.]+)", out18).group(1)),
+        "V0_RP": float(re.search(r"Value at t_0 \(Replicating-P\)\s+= ([0-9.]+)", out20).group(1)),
+        # cell 20 labels this "Discounted Eq[V(T)]" but computes values[:, 0].mean() * exp(-r T): V0_RP discounted once more
+        "printed_discounted_V0": float(re.search(r"Discounted Eq\[V\(T\)\]\s+= ([0-9.]+)", out20).group(1)),
+    }
+
+
 def main():
     warnings.filterwarnings("ignore")
     plt = _install_stubs()
@@ -216,6 +255,7 @@ def main():
         "EO_payoff_std": 12.972705, "EO_payoff_max": 100.871992, "EO_prob_otm": 0.3293,
         "MTS_mean_Y_T": 2.227189, "brownian_get_W_5_1": [0, 1.62434536, 1.01258895, 0.4844172, -0.58855142],
     }
+    summary["notebook_fit_log"] = notebook_fit_log()
     with open(os.path.join(OUT, "summary.json"), "w") as f:
         json.dump(summary, f, indent=1, sort_keys=True)
     print(json.dumps(summary, indent=1, sort_keys=True))
