@@ -388,9 +388,14 @@ def test_notebooks_config_follows_its_saved_keras_log(cuda, golden_dir, mode):
     sums, _ = orp_b200.payoff_sums(tm, [100.0], [-1], "call", values_out=vals, value_scale=1 / S0)
     disc = float(np.exp(-r) * sums[0] / 4096)
     res = orp_b200.fit_replication(tm, bond, vals, net="eo", scale=S0, mode=mode, batch_size=512, shuffle_seed=1234,
-                                   steps_per_epoch=8)
+                                   steps_per_epoch=8, var_quantiles=(.98, .99))
     steps = res["steps"]
     assert len(steps) == 52
+    # the "VaR: ... (98%), ... (99%)" line the reference prints after every step (RP.py:122): quantiles of the residuals
+    var_ours, var_theirs = np.array([st["VaR"] for st in steps]), np.array(log["VaR_98_99"])
+    var_ratio = var_ours.mean(axis=0) / var_theirs.mean(axis=0)
+    print(mode, "VaR ratio", var_ratio, "first", var_ours[0], var_theirs[0], "last", var_ours[-1], var_theirs[-1])
+    assert np.abs(var_ratio - 1).max() < 0.10, var_ratio
     theirs = np.array(log["fit_last_epoch_loss"])
     ours = np.array([st["loss"] for st in steps])
     ep_ours, ep_theirs = sum(st["epochs_run"] for st in steps[1:]), sum(log["epochs_per_fit"][1:])
