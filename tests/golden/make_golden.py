@@ -238,6 +238,27 @@ def notebook_fit_log():
     }
 
 
+def notebook_rp_log():
+    """Saved output of ``RP.Replicating_Portfolio(parameters)`` and ``RP.Replicating_Portfolio_SV(sv_parameters)`` in
+    ``Multi Time Step.ipynb`` (cells 28 and 32): the ``>> Y_(t) = ..., N_(t) = ...`` line of every rebalancing step
+    (means of the simulated fund and survivor columns: path side, reproducible to the printed digits), the
+    ``model.evaluate`` loss and the VaR line of every step, and the returned hedge weights (fit side: statistical)."""
+    import re
+    with open(os.path.join(REF, "Multi Time Step.ipynb")) as f:
+        cells = json.load(f)["cells"]
+    out = {}
+    for tag, i in (("rp", 28), ("rp_sv", 32)):
+        txt = "".join("".join(o.get("text", [])) for o in cells[i].get("outputs", []) if "text" in o)
+        out[tag] = {
+            "step_lines": re.findall(r">> Y_\([0-9.]+\) = [0-9.]+, N_\([0-9.]+\) = [0-9.]+", txt),
+            "evaluate_loss": [float(x) for x in re.findall(r"8/8 \[=+\] - [^\n]*? loss: ([0-9.e+-]+) - mae", txt)],
+            "VaR_98_99": [[float(a), float(b)] for a, b in re.findall(r"VaR: (-?[0-9.]+) \(98%\),\s+(-?[0-9.]+) \(99%\)", txt)],
+            "phi0": int(re.search(r"Phi t=0 : ([0-9,]+)", txt).group(1).replace(",", "")),
+            "psi0": int(re.search(r"Psi t=0 : ([0-9,]+)", txt).group(1).replace(",", "")),
+        }
+    return out
+
+
 def main():
     warnings.filterwarnings("ignore")
     plt = _install_stubs()
@@ -256,6 +277,7 @@ def main():
         "MTS_mean_Y_T": 2.227189, "brownian_get_W_5_1": [0, 1.62434536, 1.01258895, 0.4844172, -0.58855142],
     }
     summary["notebook_fit_log"] = notebook_fit_log()
+    summary["notebook_rp_log"] = notebook_rp_log()
     with open(os.path.join(OUT, "summary.json"), "w") as f:
         json.dump(summary, f, indent=1, sort_keys=True)
     print(json.dumps(summary, indent=1, sort_keys=True))

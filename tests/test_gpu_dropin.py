@@ -9,6 +9,9 @@ installed here): its saved outputs are phi0 = 634,349 / psi0 = 350,176 from ``RP
 in phi0; the weights trade off against each other along the value line, the value is the well-determined quantity).
 """
 import importlib
+import json
+import os
+import re
 from math import ceil
 
 import numpy as np
@@ -41,20 +44,43 @@ def _check(phi, psi, ref_phi, ref_psi):
     assert abs(phi / ref_phi - 1) < 0.12 and abs(psi / ref_psi - 1) < 0.12, (phi, psi)
 
 
-def test_replicating_portfolio_dropin_notebook_call(cuda, capsys):
+def _notebook_log(golden_dir, tag):
+    with open(os.path.join(golden_dir, "summary.json")) as f:
+        return json.load(f)["notebook_rp_log"][tag]
+
+
+def _check_prints(out, log):
+    """stdout of the call against what the reference's own run left in the saved notebook (``summary.json:
+    notebook_rp_log``).  The ``>> Y_(t) = ..., N_(t) = ...`` lines are means of the simulated fund and survivor columns:
+    path side, so they must be the notebook's lines CHARACTER FOR CHARACTER (40 of them, in order).  The VaR lines
+    come from the fit: same count and format, and the same size — the notebook's 98 % / 99 % residual quantiles lie
+    within +-0.011 of zero at every step (network units, Y = 1), ours must too."""
+    assert "reduction = 25" in out                                             # RP.py:92
+    assert re.findall(r">> Y_\([0-9.]+\) = [0-9.]+, N_\([0-9.]+\) = [0-9.]+", out) == log["step_lines"]      # RP.py:194
+    var = np.array([[float(a), float(b)] for a, b in re.findall(r"VaR: (-?[0-9.]+) \(98%\),\s+(-?[0-9.]+) \(99%\)", out)])
+    theirs = np.array(log["VaR_98_99"])
+    assert var.shape == theirs.shape == (40, 2)                               # one per rebalancing step (RP.py:122)
+    assert (var[:, 0] <= var[:, 1]).all()
+    assert np.abs(var).max() < 2 * np.abs(theirs).max(), (np.abs(var).max(), np.abs(theirs).max())
+
+
+def test_replicating_portfolio_dropin_notebook_call(cuda, capsys, golden_dir):
     import Replicating_Portfolio as RP
     importlib.reload(RP)                                                      # the notebook reloads the module
     phi, psi = RP.Replicating_Portfolio(dict(PARAMETERS))
-    out = capsys.readouterr().out
-    assert "reduction = 25" in out and ">> Y_(" in out                        # the reference's prints (RP.py:92, :194)
-    assert out.count("VaR: ") == 40 and "(98%)" in out and "(99%)" in out       # one per rebalancing step (RP.py:122)
-    _check(phi, psi, 634_349, 350_176)
+    log = _notebook_log(golden_dir, "rp")
+    _check_prints(capsys.readouterr().out, log)
+    _check(phi, psi, log["phi0"], log["psi0"])
+    assert (log["phi0"], log["psi0"]) == (634_349, 350_176)
 
 
-def test_replicating_portfolio_sv_dropin_notebook_call(cuda):
+def test_replicating_portfolio_sv_dropin_notebook_call(cuda, capsys, golden_dir):
     import Replicating_Portfolio as RP
-    phi, psi = RP.Replicating_Portfolio_SV(dict(SV_PARAMETERS, verbose=False))
-    _check(phi, psi, 626_123, 371_854)
+    phi, psi = RP.Replicating_Portfolio_SV(dict(SV_PARAMETERS))
+    log = _notebook_log(golden_dir, "rp_sv")
+    _check_prints(capsys.readouterr().out, log)
+    _check(phi, psi, log["phi0"], log["psi0"])
+    assert (log["phi0"], log["psi0"]) == (626_123, 371_854)
 
 
 def test_replicating_portfolio_dropin_with_device_survivors(cuda):
