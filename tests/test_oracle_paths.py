@@ -107,3 +107,29 @@ def test_minus_inf_propagation():
     assert S[0, 235] > 0 and np.all(S[0, 236:] == 0.0) and np.all(np.isfinite(S[1]))
     Y = paths.simulate_window("gbm_arith", p, 253, 2_631_230, 1)
     assert Y[0, 236] == -np.inf and np.all(~np.isfinite(Y[0, 236:]))
+
+
+@pytest.mark.parametrize("tag", ["rp", "rp_sv"])
+def test_step_lines_of_the_saved_notebook_run(golden_dir, tag):
+    """``Multi Time Step.ipynb`` cells 28 / 32 saved what ``RP.Replicating_Portfolio(_SV)`` printed at every rebalancing
+    step: ``>> Y_(t) = mean of the fund column, N_(t) = ...`` (RP.py:194).  The oracle's paths on the notebook's parameters
+    must give the 40 fund means digit for digit (three decimals as printed; the SV cell's dict literal has two 'c' keys,
+    the last one, 0.075, is what the module saw)."""
+    import re
+    with open(os.path.join(golden_dir, "summary.json")) as f:
+        log = json.load(f)["notebook_rp_log"][tag]
+    d = paths.n_time_steps_of(10, 1 / 100)
+    if tag == "rp":
+        Y = paths.simulate_window("gbm_arith", dict(S0=1.0, mu=0.09464, sigma=0.15965, dt=1 / 100), d, 0, 4096)
+    else:
+        Y = paths.simulate_window("sv", dict(S0=1.0, mu=0.09620, s0=0.16679, a=0.0033281299103885727,
+                                             b=0.1562947229160206, c=0.075, dt=1 / 100), d, 0, 4096)
+    red, cols, n_red = paths.reduction_of(d, 10, 1 / 4)
+    assert red == 25 and n_red == 41
+    means = Y[:, cols].mean(axis=0)
+    printed = [re.match(r">> Y_\(([0-9.]+)\) = ([0-9.]+),", line).groups() for line in log["step_lines"]]
+    assert len(printed) == 40
+    for k, (t, y) in enumerate(printed):                          # the loop runs backwards from t = T
+        t_i = n_red - 2 - k
+        assert f"{(t_i + 1) * 0.25:.2f}" == t
+        assert f"{means[t_i + 1]:.3f}" == y, (t, means[t_i + 1], y)
