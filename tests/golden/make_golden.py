@@ -256,6 +256,15 @@ def notebook_rp_log():
             "phi0": int(re.search(r"Phi t=0 : ([0-9,]+)", txt).group(1).replace(",", "")),
             "psi0": int(re.search(r"Psi t=0 : ([0-9,]+)", txt).group(1).replace(",", "")),
         }
+    # cell 29: the same call for five volatilities; cell 30 shows the returned weights as a table
+    txt = "".join("".join(o.get("text", [])) for o in cells[29].get("outputs", []) if "text" in o)
+    parts = re.split(r">>(0\.\d+)-+", txt)
+    table = "".join(cells[30]["outputs"][0]["data"]["text/plain"])
+    rows = {float(a): (float(b), float(c)) for a, b, c in re.findall(r"^(0\.\d+)\s+([0-9.]+)\s+([0-9.]+)\s", table, re.M)}
+    out["sigma_sweep"] = {
+        sig: {"step_lines": re.findall(r">> Y_\([0-9.]+\) = [0-9.]+, N_\([0-9.]+\) = [0-9.]+", body),
+              "phi0": rows[float(sig)][0], "psi0": rows[float(sig)][1]}
+        for sig, body in zip(parts[1::2], parts[2::2])}
     return out
 
 

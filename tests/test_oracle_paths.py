@@ -109,7 +109,7 @@ def test_minus_inf_propagation():
     assert Y[0, 236] == -np.inf and np.all(~np.isfinite(Y[0, 236:]))
 
 
-@pytest.mark.parametrize("tag", ["rp", "rp_sv"])
+@pytest.mark.parametrize("tag", ["rp", "rp_sv", "0.05", "0.1", "0.15", "0.2", "0.3"])
 def test_step_lines_of_the_saved_notebook_run(golden_dir, tag):
     """``Multi Time Step.ipynb`` cells 28 / 32 saved what ``RP.Replicating_Portfolio(_SV)`` printed at every rebalancing
     step: ``>> Y_(t) = mean of the fund column, N_(t) = ...`` (RP.py:194).  The oracle's paths on the notebook's parameters
@@ -117,10 +117,12 @@ def test_step_lines_of_the_saved_notebook_run(golden_dir, tag):
     the last one, 0.075, is what the module saw)."""
     import re
     with open(os.path.join(golden_dir, "summary.json")) as f:
-        log = json.load(f)["notebook_rp_log"][tag]
+        log = json.load(f)["notebook_rp_log"]
+    log = log[tag] if tag in log else log["sigma_sweep"][tag]    # cell 29: the same call for five volatilities
     d = paths.n_time_steps_of(10, 1 / 100)
-    if tag == "rp":
-        Y = paths.simulate_window("gbm_arith", dict(S0=1.0, mu=0.09464, sigma=0.15965, dt=1 / 100), d, 0, 4096)
+    if tag != "rp_sv":
+        sigma = 0.15965 if tag == "rp" else float(tag)
+        Y = paths.simulate_window("gbm_arith", dict(S0=1.0, mu=0.09464, sigma=sigma, dt=1 / 100), d, 0, 4096)
     else:
         Y = paths.simulate_window("sv", dict(S0=1.0, mu=0.09620, s0=0.16679, a=0.0033281299103885727,
                                              b=0.1562947229160206, c=0.075, dt=1 / 100), d, 0, 4096)
