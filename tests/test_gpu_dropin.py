@@ -88,3 +88,19 @@ def test_replicating_portfolio_dropin_with_device_survivors(cuda):
     import Replicating_Portfolio as RP
     phi, psi = RP.Replicating_Portfolio(dict(PARAMETERS, verbose=False, survivors='device'))
     _check(phi, psi, 634_349, 350_176)
+
+
+@pytest.mark.parametrize("sigma", ["0.05", "0.1", "0.15", "0.2", "0.3"])
+def test_replicating_portfolio_dropin_volatility_sweep(cuda, capsys, golden_dir, sigma):
+    """``Multi Time Step.ipynb`` cell 29: the same call for five volatilities.  Step lines character for character; the
+    t = 0 portfolio value phi0 + psi0 against the table of cell 30 (the weights themselves trade off along the value
+    line: at sigma = 0.05 the notebook holds 896,236 / 14,489, at 0.3 687,850 / 534,581)."""
+    import Replicating_Portfolio as RP
+    phi, psi = RP.Replicating_Portfolio(dict(PARAMETERS, sigma=float(sigma)))
+    log = _notebook_log(golden_dir, "sigma_sweep")[sigma]
+    out = capsys.readouterr().out
+    assert re.findall(r">> Y_\([0-9.]+\) = [0-9.]+, N_\([0-9.]+\) = [0-9.]+", out) == log["step_lines"]
+    v, ref_v = phi + psi, log["phi0"] + log["psi0"]
+    print(f"sigma {sigma}: phi {phi:,.0f} psi {psi:,.0f} value {v:,.0f}  notebook {log['phi0']:,.0f} {log['psi0']:,.0f} {ref_v:,.0f}  ratio {v / ref_v:.4f}")
+    # one TensorFlow run per volatility in the notebook, one here: 10 % (measured +3.5, +6.1, +0.6, +0.9, -6.9 % at sigma = 0.05 .. 0.3)
+    assert abs(v / ref_v - 1) < 0.10, (phi, psi, v, ref_v)
