@@ -115,14 +115,15 @@ enum { ORP_PAYOFF_CALL = 0, ORP_PAYOFF_PUT = 1, ORP_PAYOFF_FLOOR = 2 };
 /* Replaces the payoff and summary block: CALL/PUT European Options.ipynb cell 8 (raw 328-329, 344, 347),
  * FLOOR Replicating_Portfolio.py:88-89, means :185.  For option j: sum_i payoff(S[cols[j]][i], strikes[j])
  * and the out-of-the-money count (CALL/PUT: payoff <= 0; FLOOR: S < s0).
- * d_paths time-major [*][ld], dtype as written by orp_paths.  d_sums[n_opt], d_otm[n_opt] (fp64).
+ * d_paths time-major [n_cols][ld], dtype as written by orp_paths; every cols[j] must lie in [0, n_cols) (ORP_E_VALUE
+ * otherwise: the reference's indexing would raise IndexError).  d_sums[n_opt], d_otm[n_opt] (fp64).
  * d_values_out (optional, fp32 [count]): payoff of option 0 times value_scale — values[:, -1] of
  * Replicating_Portfolio.py:184 / European Options.ipynb cell 13.
  * d_scratch: orp_payoff_scratch_bytes(n_opt) bytes of device scratch (per-block partial sums; the two-stage
  * fixed-order reduction makes the result independent of scheduling). */
 uint64_t orp_payoff_scratch_bytes(int n_opt);
 int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, uint64_t count, int kind, int n_opt,
-                      const double* strikes, const int32_t* cols, double s0, double value_scale,
+                      const double* strikes, const int32_t* cols, int32_t n_cols, double s0, double value_scale,
                       float* d_values_out, double* d_sums, double* d_otm, void* d_scratch, void* stream);
 
 /* No counterpart in the reference.  Same computation and results as orp_payoff_reduce for callers that cannot
@@ -140,7 +141,7 @@ int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, uint64_t coun
  *   - the entry point itself never calls cudaMalloc / cudaFree or any allocating routine. */
 #define ORP_PAYOFF_NOALLOC_MAX_OPTIONS 8
 int orp_payoff_reduce_noalloc(const void* d_paths, int dtype, uint64_t ld, uint64_t count, int kind, int n_opt,
-                              const double* strikes, const int32_t* cols, double s0, double value_scale,
+                              const double* strikes, const int32_t* cols, int32_t n_cols, double s0, double value_scale,
                               float* d_values_out, double* d_sums, double* d_otm, void* stream);
 
 /* ---------------------------------------------------------------- a-9/10/11  replicating-portfolio fit (device) */
@@ -245,7 +246,9 @@ int orp_fit_end(int net, float* d_params, double* d_state, void* stream);
 
 /* Replaces model.predict(X0) / get_phi_psi_VaR means (Replicating_Portfolio.py:212, 103-115, 229-235):
  * d_values_out[i] = phi_i * S_t * inv_scale + psi_i * B_t * inv_scale (fp32), and
- * d_sums[4] = (sum V, sum phi, sum psi, sum |target - V(prices at t+1)|). */
+ * d_sums[5] = (sum V, sum phi, sum psi, sum |y - V1|, sum |y - V1| / max(|y|, 1e-7)) with y = target and
+ * V1 = V(prices at t+1): the last two are the 'mae' and 'mape' / 100 metrics of model1.evaluate (Replicating_Portfolio.py:215)
+ * before the division by the path count. */
 int orp_fit_predict(const orp_fit_batch* b, const float* d_params, float* d_values_out, double* d_sums,
                     void* d_scratch, void* stream);
 

@@ -466,15 +466,19 @@ __device__ __forceinline__ int scattered_index(int i, int lane) {
 // shared memory -> sum over the 8 warps in warp order -> dst[index * stride] (index = k for the gradient of
 // parameter k, ORP_FIT_MAX_PARAMS for the loss, + 1 for the count).  Shared by every driver of the fit.
 // tag != 0: every entry is written as two 8-byte words {low half, tag}, {high half, tag} (dst counts 16-byte
-// entries), so that a reader polling for `tag` needs no barrier and no fence (8-byte stores are single-copy atomic).
+// entries), so that a reader polling for `tag` needs no barrier and no fence (8-byte accesses are single-copy atomic).
 __device__ __forceinline__ void st_tagged(double* entry, double val, unsigned int tag) {
-    asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(entry), "r"((unsigned int)__double2loint(val)), "r"(tag),
-                 "r"((unsigned int)__double2hiint(val)), "r"(tag) : "memory");
+    // two 8-byte elements {value half (low 32 bits), tag (high 32 bits)}: each element is ONE 64-bit access in the
+    // PTX memory model (a .v4.u32 would be four independent 4-byte accesses), so a half can never be seen with a
+    // newer tag than its value
+    const unsigned long long t = (unsigned long long)tag << 32;
+    const unsigned long long e0 = t | (unsigned int)__double2loint(val), e1 = t | (unsigned int)__double2hiint(val);
+    asm volatile("st.volatile.global.v2.b64 [%0], {%1, %2};" ::"l"(entry), "l"(e0), "l"(e1) : "memory");
 }
 __device__ __forceinline__ uint4 ld_tagged(const double* entry) {
-    uint4 v;
-    asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(entry) : "memory");
-    return v;
+    unsigned long long e0, e1;
+    asm volatile("ld.volatile.global.v2.b64 {%0, %1}, [%2];" : "=l"(e0), "=l"(e1) : "l"(entry) : "memory");
+    return make_uint4((unsigned int)e0, (unsigned int)(e0 >> 32), (unsigned int)e1, (unsigned int)(e1 >> 32));   // {low, tag, high, tag}
 }
 
 template <int NET>
@@ -1017,6 +1021,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
 }
 
 // a-10 / a-11: roll-back values at prices@t and the hedge-weight sums.
+constexpr int kPredictSums = 5;      // sum V, sum phi, sum psi, sum |y - V1|, sum |y - V1| / max(|y|, 1e-7)
 template <int NET, typename T>
 __global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitArgs a, const float* __restrict__ params,
                                                                   float* __restrict__ values_out, double* __restrict__ partials) {
@@ -1025,7 +1030,7 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitAr
     load_weights<NET>(s_w, params, threadIdx.x, kFitThreads);
     __syncthreads();
     const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
-    double sv = 0.0, sphi = 0.0, spsi = 0.0, sae = 0.0;
+    double sv = 0.0, sphi = 0.0, spsi = 0.0, sae = 0.0, sape = 0.0;
     // One sample per thread and iteration (memory-bound: occupancy at 64 registers beats weight reuse here); the
     // loads of the thread's NEXT sample are issued before the arithmetic of the current one, which doubles the bytes
     // in flight per SM (32 warps x 20 B x 32 lanes alone do not cover the HBM latency-bandwidth product).
@@ -1054,22 +1059,26 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitAr
         }
         if (values_out) values_out[i] = v0[0];
         sv += v0[0]; sphi += phi[0]; spsi += psi[0];
-        if (a.target) sae += fabsf(tgt - v1);                                 // 'mae' metric of model.evaluate(X1, ...)
+        if (a.target) {                                                       // metrics of model.evaluate(X1, ...), RP.py:215
+            const float ae = fabsf(tgt - v1);
+            sae += ae;                                                        // 'mae'
+            sape += ae / fmaxf(fabsf(tgt), 1e-7f);                            // 'mape' (Keras: |y - v| / max(|y|, epsilon), x 100 on the host)
+        }
     }
-    __shared__ double s_red[kFitThreads / 32][4];
+    __shared__ double s_red[kFitThreads / 32][kPredictSums];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    double q[4] = {sv, sphi, spsi, sae};
+    double q[kPredictSums] = {sv, sphi, spsi, sae, sape};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < kPredictSums; ++k) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) q[k] += __shfl_down_sync(0xffffffffu, q[k], o);
         if (lane == 0) s_red[warp][k] = q[k];
     }
     __syncthreads();
-    if (threadIdx.x < 4) {
+    if (threadIdx.x < kPredictSums) {
         double t = 0.0;
         for (int w = 0; w < kFitThreads / 32; ++w) t += s_red[w][threadIdx.x];
-        partials[(size_t)blockIdx.x * 4 + threadIdx.x] = t;
+        partials[(size_t)blockIdx.x * kPredictSums + threadIdx.x] = t;
     }
 }
 
@@ -1089,7 +1098,7 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_residual_kernel(const FitA
         net_forward<NET, 1>(s_wa, x, s_t1, a.b_t1, act, phi, psi, v1);          // features at t, prices at t+1 (X1)
         float res = a.target[i] - v1[0];
         if (a.skip) {                                      // opt-in: same rule as the fit — such a path has no residual
-            bool fin = isfinite(s_t) && isfinite(s_t1[0]);
+            bool fin = isfinite(s_t) && isfinite(s_t1[0]) && isfinite(a.target[i]);      // the rule of unpack_raw<SKIP>
 #pragma unroll
             for (int q = 0; q < N::IN; ++q) fin = fin && isfinite(x[0][q]);
             if (!fin) res = __int_as_float(0x7fc00000);
@@ -1102,9 +1111,9 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_residual_kernel(const FitA
 // increasing order, then a shuffle tree — independent loads instead of one chain of 512 dependent ones.
 __global__ void predict_reduce_kernel(const double* __restrict__ partials, int n_blocks, double* __restrict__ sums) {
     const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (k >= 4) return;
+    if (k >= kPredictSums) return;
     double t = 0.0;
-    for (int b = lane; b < n_blocks; b += 32) t += partials[(size_t)b * 4 + k];
+    for (int b = lane; b < n_blocks; b += 32) t += partials[(size_t)b * kPredictSums + k];
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
     if (lane == 0) sums[k] = t;
@@ -1432,9 +1441,9 @@ extern "C" int orp_fit_predict(const orp_fit_batch* b, const float* d_params, fl
     cudaStream_t st = (cudaStream_t)stream;
     uint64_t want = (a.count + kFitThreads - 1) / kFitThreads;
     // four resident blocks per SM (launch bounds), a whole number of waves: 592 blocks on B200, not 512 (3.46 per SM);
-    // their 4 partial sums each fit the 512 x kGsumLen doubles in front of the scratch header many times over
+    // their 5 partial sums each fit the 512 x kGsumLen doubles in front of the scratch header many times over
     uint64_t cap = 4ull * (uint64_t)sm_count();
-    if (cap * 4 > kScrHeader) cap = kScrHeader / 4;
+    if (cap * kPredictSums > kScrHeader) cap = kScrHeader / kPredictSums;
     const int grid = (int)(want < cap ? want : cap);
     double* partials = reinterpret_cast<double*>(d_scratch);
     const bool f64 = b->paths_dtype == ORP_F64;
@@ -1446,7 +1455,7 @@ extern "C" int orp_fit_predict(const orp_fit_batch* b, const float* d_params, fl
         else     fit_predict_kernel<ORP_NET_RP, float><<<grid, kFitThreads, 0, st>>>(a, d_params, d_values_out, partials);
     }
     ORP_LAUNCH_CHECK("fit_predict_kernel");
-    predict_reduce_kernel<<<1, 128, 0, st>>>(partials, grid, d_sums);
+    predict_reduce_kernel<<<1, 32 * kPredictSums, 0, st>>>(partials, grid, d_sums);
     ORP_LAUNCH_CHECK("predict_reduce_kernel");
     return ORP_OK;
 }

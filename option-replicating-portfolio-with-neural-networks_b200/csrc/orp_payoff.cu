@@ -179,7 +179,7 @@ extern "C" uint64_t orp_payoff_scratch_bytes(int n_opt) {
 }
 
 extern "C" int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, uint64_t count, int kind, int n_opt,
-                                 const double* strikes, const int32_t* cols, double s0, double value_scale,
+                                 const double* strikes, const int32_t* cols, int32_t n_cols, double s0, double value_scale,
                                  float* d_values_out, double* d_sums, double* d_otm, void* d_scratch, void* stream) {
     ORP_REQUIRE(d_paths && strikes && cols && d_sums && d_otm && d_scratch, "null pointer");
     ORP_REQUIRE(n_opt >= 1 && n_opt <= ORP_MAX_OPTIONS, "n_opt must be in [1, %d]", ORP_MAX_OPTIONS);
@@ -191,7 +191,7 @@ extern "C" int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, ui
     a.s0 = s0; a.value_scale = value_scale; a.values_out = d_values_out;
     a.partials = reinterpret_cast<double*>(d_scratch);
     for (int k = 0; k < n_opt; ++k) {
-        ORP_REQUIRE(cols[k] >= 0, "negative column index");
+        ORP_REQUIRE(cols[k] >= 0 && cols[k] < n_cols, "column index %d of option %d is outside [0, %d)", cols[k], k, n_cols);
         a.strikes[k] = strikes[k];
         a.cols[k] = cols[k];
     }
@@ -245,7 +245,7 @@ static int noalloc_partials(double** out) {
 }
 
 extern "C" int orp_payoff_reduce_noalloc(const void* d_paths, int dtype, uint64_t ld, uint64_t count, int kind, int n_opt,
-                                         const double* strikes, const int32_t* cols, double s0, double value_scale,
+                                         const double* strikes, const int32_t* cols, int32_t n_cols, double s0, double value_scale,
                                          float* d_values_out, double* d_sums, double* d_otm, void* stream) {
     ORP_REQUIRE(d_paths && strikes && cols && d_sums && d_otm, "null pointer");
     ORP_REQUIRE(n_opt >= 1, "n_opt must be >= 1");
@@ -264,7 +264,7 @@ extern "C" int orp_payoff_reduce_noalloc(const void* d_paths, int dtype, uint64_
     a.s0 = s0; a.value_scale = value_scale; a.values_out = d_values_out;
     a.partials = partials;
     for (int k = 0; k < n_opt; ++k) {
-        ORP_REQUIRE(cols[k] >= 0, "negative column index");
+        ORP_REQUIRE(cols[k] >= 0 && cols[k] < n_cols, "column index %d of option %d is outside [0, %d)", cols[k], k, n_cols);
         a.strikes[k] = strikes[k];
         a.cols[k] = cols[k];
     }

@@ -18,9 +18,9 @@ __device__ __forceinline__ void philox_round(uint32_t (&c)[4], uint32_t k0, uint
     c[0] = n0; c[1] = lo1; c[2] = n2; c[3] = lo0;
 }
 
-// Philox4x32-10 (Salmon et al. 2011): counter (path, step) -> one uniform in (0, 1) with 53 random bits
-__device__ __forceinline__ double philox_uniform(uint64_t path, uint32_t step, uint64_t seed) {
-    uint32_t c[4] = {(uint32_t)path, (uint32_t)(path >> 32), step, 0u};
+// Philox4x32-10 (Salmon et al. 2011): counter (path, step, sub) -> one uniform in (0, 1) with 53 random bits
+__device__ __forceinline__ double philox_uniform(uint64_t path, uint32_t step, uint64_t seed, uint32_t sub = 0u) {
+    uint32_t c[4] = {(uint32_t)path, (uint32_t)(path >> 32), step, sub};
     uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
@@ -32,24 +32,54 @@ __device__ __forceinline__ double philox_uniform(uint64_t path, uint32_t step, u
     return ((double)bits + 0.5) * (1.0 / 9007199254740992.0);
 }
 
-// D ~ Binomial(n, q) by inversion from 0 (q is a one-step death probability: n q is a few units at most); beyond
-// `cap` terms the normal approximation takes over (never reached with the reference's parameters).
-__device__ __forceinline__ double binomial_deaths(double n, double q, double u) {
+// log(k!) - [ (k + 1/2) log(k + 1) - (k + 1) + log(2 pi) / 2 ]: the tail of Stirling's series (Hoermann 1993, table + series)
+__device__ __forceinline__ double stirling_tail(double k) {
+    const double t[10] = {0.0810614667953272, 0.0413406959554092, 0.0276779256849983, 0.02079067210376509,
+                          0.0166446911898211, 0.0138761288230707, 0.0118967099458917, 0.0104112652619720,
+                          0.00925546218271273, 0.00833056343336287};
+    if (k <= 9.0) return t[(int)k];
+    const double kp = k + 1.0, k2 = kp * kp;
+    return (1.0 / 12.0 - (1.0 / 360.0 - 1.0 / 1260.0 / k2) / k2) / kp;
+}
+
+// D ~ Binomial(n, q).  Which sampler runs is decided by the mean UP FRONT (np.random.binomial does the same, and
+// handles any n): inversion from 0 while n min(q, 1-q) <= 30 — then P(D = 0) >= e^-31 cannot underflow and the
+// walk ends after a few dozen terms — and Hoermann's transformed rejection (BTRS, exact) beyond, with fresh
+// uniforms from the same counter-based stream (sub-counter = attempt).  q > 1/2 is drawn through its complement.
+__device__ __forceinline__ double binomial_deaths(double n, double q, uint64_t path, uint32_t step, uint64_t seed) {
     if (!(q > 0.0) || n <= 0.0) return 0.0;
     if (q >= 1.0) return n;
-    const double p = 1.0 - q, r = q / p;
-    double pk = exp(n * log1p(-q)), cdf = pk, k = 0.0;                 // P(D = 0) = (1 - q)^n
-    const int cap = 400;
-    for (int it = 0; it < cap && u > cdf && k < n; ++it) {
-        pk *= r * (n - k) / (k + 1.0);
-        k += 1.0;
-        cdf += pk;
+    const bool flip = q > 0.5;
+    const double pq = flip ? 1.0 - q : q, pp = 1.0 - pq;
+    double k;
+    if (n * pq <= 30.0) {
+        const double u = philox_uniform(path, step, seed), r = pq / pp;
+        double pk = exp(n * log1p(-pq)), cdf = pk;                     // P(D = 0) = (1 - q)^n
+        k = 0.0;
+        for (int it = 0; it < 400 && u > cdf && k < n; ++it) {         // 400 terms: > 40 standard deviations past the mean
+            pk *= r * (n - k) / (k + 1.0);
+            k += 1.0;
+            cdf += pk;
+        }
+    } else {
+        const double spq = sqrt(n * pq * pp), b = 1.15 + 2.53 * spq, a = -0.0873 + 0.0248 * b + 0.01 * pq;
+        const double c = n * pq + 0.5, v_r = 0.92 - 4.2 / b, r = pq / pp, alpha = (2.83 + 5.1 / b) * spq;
+        const double m = floor((n + 1.0) * pq);
+        k = rint(n * pq);                                              // only if 32 attempts all reject (p < 1e-20)
+        for (uint32_t att = 0; att < 32u; ++att) {
+            const double u = philox_uniform(path, step, seed, 2u * att) - 0.5;
+            double v = philox_uniform(path, step, seed, 2u * att + 1u);
+            const double us = 0.5 - fabs(u), kk = floor((2.0 * a / us + b) * u + c);
+            if (us >= 0.07 && v <= v_r) { k = kk; break; }
+            if (kk < 0.0 || kk > n) continue;
+            v = log(v * alpha / (a / (us * us) + b));
+            const double upper = (m + 0.5) * log((m + 1.0) / (r * (n - m + 1.0))) + (n + 1.0) * log((n - m + 1.0) / (n - kk + 1.0))
+                               + (kk + 0.5) * log(r * (n - kk + 1.0) / (kk + 1.0))
+                               + stirling_tail(m) + stirling_tail(n - m) - stirling_tail(kk) - stirling_tail(n - kk);
+            if (v <= upper) { k = kk; break; }
+        }
     }
-    if (u > cdf && k < n && pk > 0.0) {                                  // far tail or huge n q: moment-matched normal
-        const double z = normcdfinv(u), d = rint(n * q + z * sqrt(n * q * p));
-        return fmin(fmax(d, 0.0), n);
-    }
-    return k;
+    return flip ? n - k : k;
 }
 
 template <typename T>
@@ -63,7 +93,7 @@ __global__ void __launch_bounds__(256) survivors_kernel(const T* __restrict__ la
         for (int t = 1; t <= n_steps; ++t) {
             const double l = (double)lam[(size_t)t * ld + j];
             const double q = -expm1(-l * dt);                              // 1 - exp(-lambda_t dt)
-            n -= binomial_deaths(n, q, philox_uniform(start + j, (uint32_t)t, seed));
+            n -= binomial_deaths(n, q, start + j, (uint32_t)t, seed);
             if (t == next_keep) {
                 out[(size_t)col * ld_out + j] = (float)(n / n0);
                 next_keep += keep_every;

@@ -85,7 +85,7 @@ class ReplicationNet:
         self.gsum = torch.zeros(_lib.GSUM_LEN, dtype=torch.float64, device=self.device)
         # zero-filled: the persistent kernel's hand-offs are tagged with a step counter kept in this buffer
         self.scratch = torch.zeros(_lib.lib().orp_fit_scratch_bytes(), dtype=torch.uint8, device=self.device)
-        self.sums = torch.zeros(4, dtype=torch.float64, device=self.device)
+        self.sums = torch.zeros(5, dtype=torch.float64, device=self.device)
         self.launches = 0
         self.two_stage = False      # True forces grad -> [all-reduce] -> update even on one GPU (tests, multi-GPU form)
         self.persistent = True      # False: one launch per optimiser step (orp_fit_epochs) instead of one per fit
@@ -282,7 +282,7 @@ class ReplicationNet:
 
     def predict(self, batch, values_out=None):
         """``model.predict(X0)`` into ``values_out`` (fp32) and the global sums
-        ``(sum V, sum phi, sum psi, sum |y - V(X1)|)`` as a 4-vector on the host."""
+        ``(sum V, sum phi, sum psi, sum |y - V(X1)|, sum |y - V(X1)| / max(|y|, 1e-7))`` as a 5-vector on the host."""
         torch = _lib.require_cuda()
         with torch.cuda.device(self.device):
             _lib.check(_lib.lib().orp_fit_predict(C.byref(batch), _lib.ptr(self.params), _lib.ptr(values_out),
@@ -360,7 +360,8 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
             allreduce_sum_(n_ok, group)
             total = max(float(n_ok), 1.0)
         rec = dict(t_i=t_i, epochs_run=h["epochs_run"], loss=h["loss"], stopped_early=h["stopped_early"],
-                   mean_V=sums[0] / total, phi=sums[1] / total, psi=sums[2] / total, mae=sums[3] / total)
+                   mean_V=sums[0] / total, phi=sums[1] / total, psi=sums[2] / total, mae=sums[3] / total,
+                   mape=100.0 * sums[4] / total)       # Keras 'mae' / 'mape' of model1.evaluate(X1, ...), RP.py:215
         if second_model:
             b2 = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="pinball", **common)
             h2 = model.fit(b2, opt2, epochs_first if first else epochs_next, patience_first if first else patience_next,

@@ -168,7 +168,7 @@ def payoff_sums(paths_tm, strikes, columns, kind: str = "call", s0: float = 0.0,
         otm = torch.empty(n_opt, dtype=torch.float64, device=paths_tm.device)
         _lib.check(_lib.lib().orp_payoff_reduce(
             _lib.ptr(paths_tm), dt, count, count, _lib.PAYOFF[kind], n_opt, _lib.ptr(strikes_s), _lib.ptr(columns_s),
-            float(s0), float(value_scale), _lib.ptr(values_out), _lib.ptr(sums), _lib.ptr(otm),
+            int(n_cols), float(s0), float(value_scale), _lib.ptr(values_out), _lib.ptr(sums), _lib.ptr(otm),
             _lib.ptr(_payoff_scratch(paths_tm.device, n_opt)), _lib.stream_ptr()))
         if n_opt > 1 and not np.array_equal(order, np.arange(n_opt)):
             inv = torch.from_numpy(np.argsort(order)).to(paths_tm.device)

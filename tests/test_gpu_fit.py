@@ -143,6 +143,12 @@ def test_scaled_fit_tracks_oracle(cuda, net, spe):
         v0, phi, psi = ofit.forward(w, net, x, p0t)
     np.testing.assert_allclose(vals.cpu().numpy(), v0.numpy(), atol=2e-3)
     np.testing.assert_allclose(sums[:3] / n, [v0.double().mean(), phi.double().mean(), psi.double().mean()], atol=2e-3)
+    # 'mae' and 'mape' of model1.evaluate(X1, ...) (RP.py:215), with the GPU's own weights so only the metric is compared
+    with torch.no_grad():
+        v1, _, _ = ofit.forward(model.params[:model.P].cpu(), net, x, p1)
+    ae = (yt - v1).abs().double()
+    np.testing.assert_allclose(sums[3] / n, ae.mean(), rtol=1e-4)
+    np.testing.assert_allclose(100.0 * sums[4] / n, 100.0 * (ae / yt.abs().double().clamp_min(1e-7)).mean(), rtol=1e-4)
 
 
 @pytest.mark.parametrize("net,n,spe", [("eo", 70_001, 3), ("rp", 5_000, 1), ("eo", 300_000, 8)])

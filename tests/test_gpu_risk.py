@@ -126,10 +126,12 @@ def test_device_survivors_match_the_reference_draws_in_distribution(cuda):
 
 def test_device_survivors_one_step_binomial_moments(cuda):
     """One step with a constant intensity: deaths ~ Binomial(N, q); mean N q and variance N q (1 - q) over 2^18 paths,
-    for a rare-event q (the reference's regime) and for a large one (exercises the long inversion loop)."""
+    for a rare-event q (the reference's regime: inversion from 0), for large means (n q = 130, 1000 and 7e5: the exact
+    transformed-rejection sampler — the inversion's P(D = 0) underflows there and np.random.binomial handles any n) and
+    for q > 1/2 (drawn through the complement, both samplers)."""
     import orp_b200
     n_paths = 2 ** 18
-    for N, lam in ((10_000, 0.015), (500, 30.0)):
+    for N, lam in ((10_000, 0.015), (500, 30.0), (1_000_000, 0.1), (1_000_000, 120.0), (2000, 300.0), (50, 200.0)):
         dt = 0.01
         L = torch.full((2, n_paths), lam, dtype=torch.float64, device=cuda)
         frac = orp_b200.survivors(L, N, dt, seed=7)

@@ -38,7 +38,7 @@ def _both(tm, strikes, cols, kind, s0, with_values):
     dtype = _lib.F64 if tm.dtype == torch.float64 else _lib.F32
     with torch.cuda.device(dev):
         _lib.check(_lib.lib().orp_payoff_reduce_noalloc(
-            _lib.ptr(tm), dtype, count, count, _lib.PAYOFF[kind], len(k), _lib.ptr(k), _lib.ptr(c),
+            _lib.ptr(tm), dtype, count, count, _lib.PAYOFF[kind], len(k), _lib.ptr(k), _lib.ptr(c), int(n_cols),
             float(s0), 0.01, _lib.ptr(v_new), _lib.ptr(sums), _lib.ptr(otm), _lib.stream_ptr()))
     torch.cuda.synchronize(dev)
     return (s_ref, o_ref, v_ref), (sums, otm, v_new)
@@ -57,8 +57,13 @@ def test_noalloc_matches_regular_entry_point_twice_in_a_row(cuda):
         # and once more with the FLOOR payoff of Replicating_Portfolio.py:88-89
         (tm64, [100.0], [12], "floor", 100.0, True),
     ]
-    for tm, strikes, cols, kind, s0, with_values in calls:
+    for n_call, (tm, strikes, cols, kind, s0, with_values) in enumerate(calls):
+        free_before = torch.cuda.mem_get_info(cuda)[0]
         ref, new = _both(tm, strikes, cols, kind, s0, with_values)
+        if n_call > 0:
+            # from the second call on nothing may come out of the device heap: the free byte count the driver reports
+            # can only move by what THIS test allocates through torch's caching allocator (its outputs: re-used blocks)
+            assert torch.cuda.mem_get_info(cuda)[0] >= free_before - (4 << 20)
         np.testing.assert_allclose(new[0].cpu().numpy(), ref[0].cpu().numpy(), rtol=1e-9)
         assert np.array_equal(new[1].cpu().numpy(), ref[1].cpu().numpy())
         if with_values:
@@ -76,5 +81,27 @@ def test_noalloc_rejects_more_options_than_its_scratch_holds(cuda):
     out = torch.zeros(2 * n, dtype=torch.float64, device=cuda)
     with pytest.raises(ValueError, match="at most 8 options"):
         _lib.check(_lib.lib().orp_payoff_reduce_noalloc(_lib.ptr(tm), _lib.F64, tm.shape[1], tm.shape[1], 0, n, _lib.ptr(k),
-                                                        _lib.ptr(c), 100.0, 1.0, None, _lib.ptr(out), _lib.ptr(out[n:]),
+                                                        _lib.ptr(c), 5, 100.0, 1.0, None, _lib.ptr(out), _lib.ptr(out[n:]),
                                                         _lib.stream_ptr()))
+
+
+def test_noalloc_rejects_a_maturity_column_outside_the_path_array(cuda):
+    """A bad maturity index must come back as ValueError (the reference's ``paths[:, t]`` would raise IndexError), not
+    as an out-of-bounds read on the device; the same check guards the regular entry point."""
+    from orp_b200 import _lib
+    import orp_b200
+    tm = orp_b200.simulate_paths("gbm_log", dict(S0=100.0, mu=0.05, sigma=0.2, dt=0.25), m=10, steps=4,
+                                 device=cuda, time_major=True)
+    k = np.array([100.0, 100.0])
+    out = torch.zeros(4, dtype=torch.float64, device=cuda)
+    scratch = torch.zeros(_lib.lib().orp_payoff_scratch_bytes(2), dtype=torch.uint8, device=cuda)
+    for bad in ([4, 5], [-1, 4]):
+        c = np.array(bad, dtype=np.int32)
+        with pytest.raises(ValueError, match="outside"):
+            _lib.check(_lib.lib().orp_payoff_reduce_noalloc(_lib.ptr(tm), _lib.F64, tm.shape[1], tm.shape[1], 0, 2, _lib.ptr(k),
+                                                            _lib.ptr(c), 5, 100.0, 1.0, None, _lib.ptr(out), _lib.ptr(out[2:]),
+                                                            _lib.stream_ptr()))
+        with pytest.raises(ValueError, match="outside"):
+            _lib.check(_lib.lib().orp_payoff_reduce(_lib.ptr(tm), _lib.F64, tm.shape[1], tm.shape[1], 0, 2, _lib.ptr(k),
+                                                    _lib.ptr(c), 5, 100.0, 1.0, None, _lib.ptr(out), _lib.ptr(out[2:]),
+                                                    _lib.ptr(scratch), _lib.stream_ptr()))
