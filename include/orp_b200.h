@@ -287,6 +287,16 @@ int orp_select_next(const float* d_x, uint64_t n, uint32_t key, unsigned long lo
 int orp_survivors(const void* d_lambda, int dtype, uint64_t ld, uint64_t start, uint64_t count, int n_steps,
                   int keep_every, double n0, double dt, uint64_t seed, float* d_out, uint64_t ld_out, void* stream);
 
+/* ---------------------------------------------------------------- measurement support */
+
+/* No counterpart in the reference.  Launches a register-only loop of one instruction kind on every SM (2 blocks of 512
+ * threads per SM, 8 independent chains per thread, `iters` x 64 instructions per chain; 8 per chain for the MMA probe)
+ * and returns the number of WARP instructions issued; the caller times the launch with CUDA events.  bench.py uses
+ * ORP_PROBE_FFMA2 (two fp32 FMAs per lane and instruction) as the measured denominator of the fit kernel's roofline:
+ * MEASURED_PEAKS.json has no fp32 figure. */
+enum { ORP_PROBE_FFMA2 = 0, ORP_PROBE_FFMA = 1, ORP_PROBE_FADD = 2, ORP_PROBE_LOP3 = 3, ORP_PROBE_MMA_TF32 = 4 };
+int orp_probe_throughput(int kind, int iters, float* d_sink, double* warp_instructions_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

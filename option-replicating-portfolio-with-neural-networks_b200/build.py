@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "liborp_b200.so")
-SOURCES = ["orp_sobol_host.cu", "orp_paths.cu", "orp_payoff.cu", "orp_fit.cu", "orp_select.cu", "orp_survivors.cu"]
+SOURCES = ["orp_sobol_host.cu", "orp_paths.cu", "orp_payoff.cu", "orp_fit.cu", "orp_select.cu", "orp_survivors.cu", "orp_probe.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared", "-cudart", "static", "--threads", "0"]
 

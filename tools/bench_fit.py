@@ -18,8 +18,11 @@ m = int(sys.argv[1]) if len(sys.argv) > 1 else 25
 net = sys.argv[2] if len(sys.argv) > 2 else "eo"
 D = 4
 p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1.0 / 252)
-for dtype in ("float64", "float32"):
-    tm = orp_b200.simulate_paths("gbm_log", p, m=m, steps=D, dtype=dtype, time_major=True)
+for dtype in ("float64", "float32", "float32 pre-scaled"):
+    tm = orp_b200.simulate_paths("gbm_log", p, m=m, steps=D, dtype=dtype.split()[0], time_major=True)
+    inv_scale = 0.01
+    if dtype.endswith("pre-scaled"):               # what fit_replication hands to the kernels: fp32 columns already divided by S0
+        tm, inv_scale = (tm.double() * 0.01).float(), 1.0
     n = 2 ** m
     vals = torch.empty(n, dtype=torch.float32, device="cuda")
     orp_b200.payoff_sums(tm, [100.0], [-1], "call", values_out=vals, value_scale=0.01)
@@ -27,7 +30,7 @@ for dtype in ("float64", "float32"):
     f2 = torch.zeros(n, dtype=torch.float32, device="cuda") if net == "rp" else None
     model = ReplicationNet(net, init_params(net, 1234, 0.1 if net == "eo" else [0.9, 0.1]), "cuda")
     opt = Optimizer("cuda")
-    b = model.batch(tm[D - 1], tm[D], vals, 0.01, 1.0, 1.0, feat1=f1, feat2=f2)
+    b = model.batch(tm[D - 1], tm[D], vals, inv_scale, 1.0, 1.0, feat1=f1, feat2=f2)
     L = _lib.lib()
     st = _lib.stream_ptr()
     _lib.check(L.orp_fit_begin(_lib.ptr(opt.state), 10 ** 6, 10 ** 6, 0, st))
