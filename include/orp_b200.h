@@ -161,10 +161,18 @@ int orp_fit_n_params(int net);
  * (they exist from 2^22 paths on) otherwise turns the whole fit into NaN. */
 #define ORP_FIT_SKIP_NONFINITE 1
 
+/* Segments (no counterpart in the reference, which runs in one process): a batch may consist of n_seg equally long
+ * pieces of `count` samples, piece v starting seg_stride * v samples after the base pointers.  Every piece is reduced
+ * on its own (fp32 per thread, then fp64 in a fixed order) and the pieces' totals are added pairwise in piece order.
+ * With the paths cut into V = 8 virtual shards of the GLOBAL index space, a rank that holds L = V / world of them and
+ * passes them as L segments produces — after the pairwise sum over ranks — exactly the bits one GPU produces with 8
+ * segments: the fitted weights do not depend on the number of GPUs (1, 2, 4 or 8). */
+#define ORP_FIT_MAX_SEGMENTS 8
+
 typedef struct orp_fit_batch {
     int32_t net;            /* ORP_NET_* */
     int32_t loss;           /* ORP_LOSS_* */
-    int32_t paths_dtype;    /* dtype of d_s_t / d_s_t1 */
+    int32_t paths_dtype;    /* dtype of d_s_t / d_s_t1; ORP_F32 columns must already be in network units (inv_scale = 1, see orp_fit_scale_column) */
     int32_t reserved;       /* flags: ORP_FIT_SKIP_NONFINITE (0 = the reference's behaviour: NaN / inf propagate) */
     uint64_t count;         /* local paths */
     const void* d_s_t;      /* S column t   (feature, and price for the roll-back) */
@@ -174,6 +182,9 @@ typedef struct orp_fit_batch {
     const float* d_target;  /* values[:, t+1] */
     double inv_scale;       /* 1 / ADJUSTMENT_FACTOR applied to prices (EO: 1/S0; RP: 1) */
     double bond_t, bond_t1; /* B_t, B_{t+1} (Replicating_Portfolio.py:68) */
+    uint32_t n_seg;         /* segments (0 or 1: one piece of `count` samples); at most ORP_FIT_MAX_SEGMENTS */
+    uint32_t reserved2;
+    uint64_t seg_stride;    /* samples between the starts of consecutive segments (>= count) */
 } orp_fit_batch;
 
 uint64_t orp_fit_scratch_bytes(void);
@@ -235,6 +246,13 @@ int orp_peer_buffer_close(void* d_ptr);
 int orp_peer_buffer_destroy(void* d_buf);
 int orp_fit_run_peers(const orp_fit_batch* b, int n_parts, float* d_params, double* d_state, double* d_gsum,
                       void* d_scratch, int n_epochs, int rank, int world, void* const* d_peer_buffers, void* stream);
+
+/* A price column in network units: d_out[i] = (float)((double)d_in[i] * inv_scale) — the division by ADJUSTMENT_FACTOR
+ * (European Options.ipynb cell 13 raw 3551-3554) followed by the cast Keras applies to float64 inputs.  The fit kernels
+ * do this themselves on the fly; a caller that runs many epochs on the same two columns converts each column once,
+ * passes the fp32 copies with paths_dtype = ORP_F32, inv_scale = 1 (and bond_t, bond_t1 already multiplied by the
+ * scale) and gets the same bits with 12 instead of 20 bytes per sample and no fp64 arithmetic in the epoch loop. */
+int orp_fit_scale_column(const void* d_in, int dtype, uint64_t count, double inv_scale, float* d_out, void* stream);
 
 /* Starts a Model.fit call: resets the early-stopping state, keeps weights and Adam moments (they persist across
  * time steps, Replicating_Portfolio.py:203-211).  use_schedule = 1 for the first fit. */

@@ -317,11 +317,34 @@ struct FitArgs {
     uint64_t count;
     float inv_scale_f; double inv_scale; float b_t, b_t1;
     int skip;                  // non-zero: samples with a non-finite input or target take no part (ORP_FIT_SKIP_NONFINITE)
+    int n_seg;                 // the batch is n_seg segments of `count` samples, segment v starting seg_stride * v samples in
+    uint64_t seg_stride;
 };
 
+// Segment v of a batch as a batch of its own (orp_fit_batch.n_seg: the virtual shards that make the fit's sums
+// independent of the number of GPUs, see reduce_partials).
+template <typename T>
+__device__ __forceinline__ FitArgs seg_args(const FitArgs& b, int v) {
+    FitArgs a = b;
+    const uint64_t off = (uint64_t)v * b.seg_stride;
+    a.s_t = reinterpret_cast<const char*>(b.s_t) + off * sizeof(T);
+    a.s_t1 = reinterpret_cast<const char*>(b.s_t1) + off * sizeof(T);
+    a.target = b.target + off;
+    if (b.feat1) a.feat1 = b.feat1 + off;
+    if (b.feat2) a.feat2 = b.feat2 + off;
+    return a;
+}
+
+// A price in network units.  fp64 columns: divide in fp64, then Keras' cast.  fp32 columns are in network units already
+// (make_args insists on inv_scale == 1 for them; orp_fit_scale_column produces them with the same fp64 division).
+template <typename T>
+__device__ __forceinline__ float to_net(T v, double inv_scale) {
+    if (sizeof(T) == 4) return (float)v;
+    return (float)((double)v * inv_scale);
+}
 template <typename T>
 __device__ __forceinline__ float load_price(const void* p, uint64_t i, double inv_scale) {
-    return (float)((double)reinterpret_cast<const T*>(p)[i] * inv_scale);     // divide in fp64, then Keras' cast
+    return to_net<T>(reinterpret_cast<const T*>(p)[i], inv_scale);
 }
 
 template <int NET, typename T>
@@ -415,17 +438,42 @@ __global__ void fit_update_kernel(int P, float* __restrict__ params, double* __r
     optimiser_step(P, params, state, gsum, flags);
 }
 
-// Fixed-order sum of the per-block partials by ONE block of 256 threads: lane l adds blocks l, l+32, ... in
-// increasing order, then a shuffle tree combines the 32 lane sums — the same association on every launch,
-// whichever block finished last.  Writes gsum and (optionally) a shared-memory copy.
-__device__ __forceinline__ void reduce_partials(const double* __restrict__ partials, int n_blocks,
+// Pairwise (balanced-tree) sum of n values in index order: ((v0 + v1) + (v2 + v3)) + ...  The sums over virtual shards
+// and over ranks use it, so that a rank holding the shards [r L, (r + 1) L) of the V = L x world shards adds its own L
+// totals first and the ranks' totals afterwards and still reproduces, bit for bit, the one-GPU sum over all V shards
+// (L and world powers of two).
+template <int MAXN>
+__device__ __forceinline__ double tree_sum(double (&v)[MAXN], int n) {
+#pragma unroll
+    for (int stride = 1; stride < MAXN; stride *= 2)
+#pragma unroll
+        for (int i = 0; i + stride < MAXN; i += 2 * stride)
+            if (i + stride < n) v[i] += v[i + stride];
+    return v[0];
+}
+
+constexpr int kMaxSeg = ORP_FIT_MAX_SEGMENTS;
+
+// Fixed-order sum of the per-block partials [segment][block][kGsumLen] by ONE block of 256 threads: per segment, lane l
+// adds blocks l, l+32, ... in increasing order and a shuffle tree combines the 32 lane sums; the segment totals are
+// then added pairwise — the same association on every launch, whichever block finished last, and on any number of
+// GPUs that hold whole segments.  Writes gsum and (optionally) a shared-memory copy.
+__device__ __forceinline__ void reduce_partials(const double* __restrict__ partials, int n_blocks, int n_seg,
                                                 double* __restrict__ gsum, double* s_copy) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int k = warp; k < kGsumLen; k += 8) {
-        double t = 0.0;
-        for (int b = lane; b < n_blocks; b += 32) t += __ldcg(partials + (size_t)b * kGsumLen + k);
+        double seg[kMaxSeg];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+        for (int v = 0; v < kMaxSeg; ++v) {
+            double t = 0.0;
+            if (v < n_seg) {
+                for (int b = lane; b < n_blocks; b += 32) t += __ldcg(partials + ((size_t)v * n_blocks + b) * kGsumLen + k);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+            }
+            seg[v] = t;
+        }
+        const double t = tree_sum<kMaxSeg>(seg, n_seg);
         if (lane == 0) { gsum[k] = t; if (s_copy) s_copy[k] = t; }
     }
 }
@@ -552,8 +600,8 @@ __device__ __forceinline__ void load_raw_any(const FitArgs& a, uint64_t i, RawSa
 
 template <int NET, typename T, bool SKIP>
 __device__ __forceinline__ bool unpack_raw(const FitArgs& a, const RawSample<NET, T>& r, float (&x)[Net<NET>::IN], float& s_t1, float& y) {
-    x[0] = (float)((double)r.s_t * a.inv_scale);          // divide in fp64, then Keras' cast
-    s_t1 = (float)((double)r.s_t1 * a.inv_scale);
+    x[0] = to_net<T>(r.s_t, a.inv_scale);
+    s_t1 = to_net<T>(r.s_t1, a.inv_scale);
     y = r.y;
     if (NET == ORP_NET_RP) { x[1] = r.f1; x[Net<NET>::IN - 1] = r.f2; }
     if (SKIP) {                                            // opt-in (own instantiation: the default loop carries none of it):
@@ -648,14 +696,18 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
     __syncthreads();
     const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
 
-    Grads<NET> g;
-    g.zero();
-    float loss = 0.f;
-    uint32_t n = 0;
     RawSample<NET, T> first[kFitUnroll<NET>];
-    load_first_tile<NET, T>(a, blockIdx.x, first);
-    accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, blockIdx.x, gridDim.x, first, g, loss, n);
-    block_reduce_to<NET>(g, loss, n, partials + (size_t)blockIdx.x * kGsum);
+    load_first_tile<NET, T>(seg_args<T>(a, 0), blockIdx.x, first);
+    for (int v = 0; v < a.n_seg; ++v) {                   // one UNIT (fp32 accumulators of this block) per segment
+        Grads<NET> g;
+        g.zero();
+        float loss = 0.f;
+        uint32_t n = 0;
+        accumulate_tiles<NET, LOSS, T, SKIP>(seg_args<T>(a, v), s_wa, blockIdx.x, gridDim.x, first, g, loss, n);
+        if (v + 1 < a.n_seg) load_first_tile<NET, T>(seg_args<T>(a, v + 1), blockIdx.x, first);
+        if (v) __syncthreads();                            // the previous unit's shared-memory totals have been read
+        block_reduce_to<NET>(g, loss, n, partials + ((size_t)v * gridDim.x + blockIdx.x) * kGsum);
+    }
     if (STEP) {
         __shared__ bool s_last;
         __shared__ double s_g[kGsumLen];
@@ -666,17 +718,17 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
         __syncthreads();
         if (!s_last) return;
         __threadfence();
-        reduce_partials(partials, (int)gridDim.x, gsum, s_g);
+        reduce_partials(partials, (int)gridDim.x, a.n_seg, gsum, s_g);
         __syncthreads();
         optimiser_step(N::P, params, state, s_g, flags);
         if (threadIdx.x == 0) *ticket = 0u;                // ready for the next launch
     }
 }
 
-__global__ void __launch_bounds__(256) fit_reduce_kernel(const double* __restrict__ partials, int n_blocks,
+__global__ void __launch_bounds__(256) fit_reduce_kernel(const double* __restrict__ partials, int n_blocks, int n_seg,
                                                          const double* __restrict__ state, double* __restrict__ gsum) {
     if (state[ST_STOP] != 0.0) return;
-    reduce_partials(partials, n_blocks, gsum, nullptr);
+    reduce_partials(partials, n_blocks, n_seg, gsum, nullptr);
 }
 
 __global__ void fit_init_kernel(double* __restrict__ state) {
@@ -715,6 +767,16 @@ __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
     return v;
 }
 
+// Hand-over polls give up after a wall-clock budget (not a retry count: host-side skew between ranks — a first-launch
+// module load, a slow collective — or a profiler's replay can stretch a healthy wait by orders of magnitude).
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+constexpr unsigned long long kPollBudgetNs = 60ull * 1000ull * 1000ull * 1000ull;      // 60 s
+__device__ __forceinline__ bool poll_expired(unsigned long long t_start) { return globaltimer_ns() - t_start > kPollBudgetNs; }
+
 // Optional phase timestamps (build with -DORP_FIT_TRACE; tools/trace_fit.py): blocks 0 and G-1 write %globaltimer at
 // eight points of each of the first 512 optimiser steps into the 64 KB tail of the scratch buffer.
 #ifdef ORP_FIT_TRACE
@@ -732,10 +794,11 @@ __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
 #endif
 
 struct RunArgs;
-template <typename T> __device__ __forceinline__ FitArgs part_args(const RunArgs& r, int k, uint32_t G, uint32_t& g_k);
+template <typename T> __device__ __forceinline__ FitArgs part_args(const RunArgs& r, int v, int k, uint32_t G, uint32_t& g_k);
 
 struct RunArgs {
-    FitArgs a;                 // the whole batch; part k = samples [k * per, min((k + 1) * per, count))
+    FitArgs a;                 // the whole batch: a.n_seg segments of a.count samples; part k of a segment = its samples
+                               // [k * per, min((k + 1) * per, count)); optimiser step k sees part k of EVERY segment
     uint64_t per;
     int n_parts, n_epochs, max_blocks_per_part, unroll;
     int rank, world;           // world = 0: single GPU, no exchange
@@ -758,18 +821,18 @@ constexpr int kPeerDoubles = kPeerSlots + 2 * kPeerMaxWorld * kGsumLen * 2;
 // Scratch layout of the persistent fit (in doubles from the start of d_scratch; the first region belongs to the
 // per-step drivers).  The scratch must be ZERO-FILLED once before its first use: the tags below count up from the
 // step counter kept in its header and must never meet stale memory that happens to carry a future tag.
-constexpr int kLLBlocks = 512;                                              // grid size limit (fit_blocks caps at 512)
-constexpr size_t kScrHeader = 512ull * kGsumLen;                            // word 0 (uint32): optimiser steps done with this scratch
-constexpr size_t kScrLLPart = kScrHeader + 16;                              // tagged block totals [2][kGsumLen][kLLBlocks][2]
-constexpr size_t kScrLLFinal = kScrLLPart + 2ull * kGsumLen * kLLBlocks * 2;    // tagged totals [2][kPeerMaxWorld][kGsumLen][2] (one GPU)
+constexpr int kLLBlocks = 256;                                              // grid size limit (fit_blocks caps at it)
+constexpr size_t kScrHeader = (size_t)kMaxSeg * kLLBlocks * kGsumLen;       // (per-step drivers' partials in front); word 0 (uint32): optimiser steps done with this scratch
+constexpr size_t kScrLLPart = kScrHeader + 16;                              // tagged block totals [2][kMaxSeg][kGsumLen][kLLBlocks][2]
+constexpr size_t kScrLLFinal = kScrLLPart + 2ull * kMaxSeg * kGsumLen * kLLBlocks * 2;    // tagged totals [2][kPeerMaxWorld][kGsumLen][2] (one GPU)
 constexpr size_t kScrDoubles = kScrLLFinal + 2ull * kPeerMaxWorld * kGsumLen * 2;
 
-// Batch k of the epoch and the number of blocks that work on it (the grid orp_fit_grad would launch for it).
+// Part k of segment v and the number of blocks that work on it (the grid orp_fit_grad would launch for it).
 template <typename T>
-__device__ __forceinline__ FitArgs part_args(const RunArgs& r, int k, uint32_t G, uint32_t& g_k) {
+__device__ __forceinline__ FitArgs part_args(const RunArgs& r, int v, int k, uint32_t G, uint32_t& g_k) {
     FitArgs a = r.a;
-    const uint64_t off = (uint64_t)k * r.per;
-    a.count = min(r.per, r.a.count - off);
+    const uint64_t in_seg = (uint64_t)k * r.per, off = (uint64_t)v * r.a.seg_stride + in_seg;
+    a.count = min(r.per, r.a.count - in_seg);
     a.s_t = reinterpret_cast<const char*>(r.a.s_t) + off * sizeof(T);
     a.s_t1 = reinterpret_cast<const char*>(r.a.s_t1) + off * sizeof(T);
     a.target = r.a.target + off;
@@ -818,7 +881,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     RawSample<NET, T> first[kFitUnroll<NET>];
     {
         uint32_t g0;
-        const FitArgs a0 = part_args<T>(r, 0, G, g0);
+        const FitArgs a0 = part_args<T>(r, 0, 0, G, g0);
         load_first_tile<NET, T>(a0, blockIdx.x, first);
     }
     for (int e = 0; e < r.n_epochs && alive; ++e) {
@@ -829,28 +892,34 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             const unsigned int barriers_done_for_trace = barriers;
 #endif
             ORP_TRACE(0);
-            uint32_t g_k;
-            const FitArgs a = part_args<T>(r, k, G, g_k);
-            Grads<NET> g;
-            g.zero();
-            float loss = 0.f;
-            uint32_t n = 0;
-            if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, blockIdx.x, g_k, first, g, loss, n);
-            ORP_TRACE(1);
-
-            // ---- block total -> tagged entry [parity][column][block] (blocks without tiles in this batch publish nothing)
+            // ---- one UNIT per segment: this block's tiles of part k of segment v -> fp32 accumulators -> block total
+            //      -> tagged entry [parity][segment][column][block] (blocks without tiles in this part publish nothing)
             ++barriers;
             const unsigned int tag = tag0 + barriers;                          // never 0; grows across launches
             const unsigned int par = tag & 1u;
-            double* const part = ll_part + (size_t)par * kGsumLen * kLLBlocks * 2;
-            if (blockIdx.x < g_k) block_partial<NET>(g, loss, n, s_red, part + 2 * blockIdx.x, kLLBlocks, tag);
-            // request the first tile of the NEXT optimiser step now: the loads land while this block waits for the
-            // other blocks' totals (wasted only when the fit stops here)
-            {
-                uint32_t g_next;
-                const FitArgs a_next = part_args<T>(r, k + 1 < r.n_parts ? k + 1 : 0, G, g_next);
-                load_first_tile<NET, T>(a_next, blockIdx.x, first);
+            const int n_seg = r.a.n_seg;
+            double* const part = ll_part + (size_t)par * kMaxSeg * kGsumLen * kLLBlocks * 2;
+            uint32_t g_k = 0;
+            for (int sg = 0; sg < n_seg; ++sg) {
+                const FitArgs a = part_args<T>(r, sg, k, G, g_k);
+                Grads<NET> g;
+                g.zero();
+                float loss = 0.f;
+                uint32_t n = 0;
+                if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, blockIdx.x, g_k, first, g, loss, n);
+                // request the first tile of the NEXT unit now (next segment, or part k + 1 of segment 0: those loads land
+                // while this block waits for the other blocks' totals; wasted only when the fit stops here)
+                {
+                    uint32_t g_next;
+                    const bool same_step = sg + 1 < n_seg;
+                    const FitArgs a_next = part_args<T>(r, same_step ? sg + 1 : 0, same_step ? k : (k + 1 < r.n_parts ? k + 1 : 0), G, g_next);
+                    load_first_tile<NET, T>(a_next, blockIdx.x, first);
+                }
+                if (sg) __syncthreads();                                        // s_red of the previous unit has been read
+                if (blockIdx.x < g_k)
+                    block_partial<NET>(g, loss, n, s_red, part + ((size_t)sg * kGsumLen * kLLBlocks + blockIdx.x) * 2, kLLBlocks, tag);
             }
+            ORP_TRACE(1);
             ORP_TRACE(2);
             // the step's learning rate: Adam bias terms from a table that all threads refill together every 256 steps
             if (((barriers - 1u) & (kFitThreads - 1u)) == 0u) {
@@ -881,30 +950,39 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             //  the extra tile and finish last — they should not also have a column to add up)
             for (int q = (int)(G - 1 - blockIdx.x) + warp * (int)G; q < P + 2; q += 8 * (int)G) {
                 const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
-                const double* col = part + (size_t)qq * kLLBlocks * 2;
-                double t = 0.0;
+                double seg[kMaxSeg];
                 bool ok = true;
-                for (uint32_t b0 = 0; b0 < g_k && ok; b0 += 160) {
-                    // every retry re-reads ALL of this lane's entries at once (independent loads: one L2 round trip per
-                    // retry), so the total is ready at most two round trips after the last block has published
-                    uint4 v[5];
-                    unsigned int spins = 0;
-                    for (;;) {
-                        bool ready = true;
+                const unsigned long long t_start = globaltimer_ns();
 #pragma unroll
-                        for (int j = 0; j < 5; ++j) v[j] = ld_tagged(col + 2 * (size_t)min(b0 + 32 * j + lane, g_k - 1));
+                for (int sv = 0; sv < kMaxSeg; ++sv) {                         // per segment: the blocks' entries in the fixed order
+                    double t = 0.0;
+                    if (sv < n_seg && ok) {
+                        const double* col = part + ((size_t)sv * kGsumLen + qq) * kLLBlocks * 2;
+                        for (uint32_t b0 = 0; b0 < g_k && ok; b0 += 160) {
+                            // every retry re-reads ALL of this lane's entries at once (independent loads: one L2 round trip
+                            // per retry), so the total is ready at most two round trips after the last block has published
+                            uint4 v[5];
+                            unsigned int spins = 0;
+                            for (;;) {
+                                bool ready = true;
 #pragma unroll
-                        for (int j = 0; j < 5; ++j) ready = ready && v[j].y == tag && v[j].w == tag;
-                        if (ready) break;
-                        if (++spins > (1u << 22) || (((spins & 255u) == 0u) && ld_acquire_u32(abort_flag) != 0u)) { ok = false; break; }
+                                for (int j = 0; j < 5; ++j) v[j] = ld_tagged(col + 2 * (size_t)min(b0 + 32 * j + lane, g_k - 1));
+#pragma unroll
+                                for (int j = 0; j < 5; ++j) ready = ready && v[j].y == tag && v[j].w == tag;
+                                if (ready) break;
+                                if (((++spins & 255u) == 0u) && (poll_expired(t_start) || ld_acquire_u32(abort_flag) != 0u)) { ok = false; break; }
+                            }
+#pragma unroll
+                            for (int j = 0; j < 5; ++j) t += b0 + 32 * j + lane < g_k ? __hiloint2double((int)v[j].z, (int)v[j].x) : 0.0;
+                        }
+                        ok = __all_sync(0xffffffffu, ok);
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
                     }
-#pragma unroll
-                    for (int j = 0; j < 5; ++j) t += b0 + 32 * j + lane < g_k ? __hiloint2double((int)v[j].z, (int)v[j].x) : 0.0;
+                    seg[sv] = t;
                 }
-                ok = __all_sync(0xffffffffu, ok);
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
                 if (!ok) { if (lane == 0) { atomicExch(abort_flag, 1u); s_peer_ok = 0; } continue; }
+                double t = tree_sum<kMaxSeg>(seg, n_seg);                      // the segments' totals, pairwise in segment order
                 t = __shfl_sync(0xffffffffu, t, 0);
                 if (lane < n_ranks) {
                     double* dst = (r.world > 0 ? r.peers[lane] + kPeerSlots : ll_final)
@@ -922,10 +1000,11 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 const int qg = (int)(blockIdx.x % (unsigned)(P + 2));
                 const int qq = qg < P ? qg : ORP_FIT_MAX_PARAMS + (qg - P);
                 const double* w = fin_mine + (((size_t)fpar * kPeerMaxWorld + (n_ranks - 1)) * kGsumLen + qq) * 2;
+                const unsigned long long t_start = globaltimer_ns();
                 unsigned int spins = 0;
                 uint4 v = ld_tagged(w);
                 while (v.y != step_id || v.w != step_id) {
-                    if (++spins > (1u << 22) || (((spins & 255u) == 0u) && ld_acquire_u32(abort_flag) != 0u)) break;     // the polls below report it
+                    if (((++spins & 255u) == 0u) && (poll_expired(t_start) || ld_acquire_u32(abort_flag) != 0u)) break;   // the polls below report it
                     v = ld_tagged(w);
                 }
             }
@@ -933,30 +1012,33 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             for (int q = tid; q < P + 2; q += kFitThreads) {
                 const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
                 const double* w0 = fin_mine + ((size_t)fpar * kPeerMaxWorld * kGsumLen + qq) * 2;
-                double t = 0.0;
-                for (int s0 = 0; s0 < n_ranks; s0 += 8) {                      // eight ranks per pass, all their entries per retry
+                double rk[kPeerMaxWorld];
+                const unsigned long long t_start = globaltimer_ns();
+#pragma unroll
+                for (int s0 = 0; s0 < kPeerMaxWorld; s0 += 8) {                // eight ranks per pass, all their entries per retry
                     uint4 v[8];
                     unsigned int spins = 0;
-                    for (;;) {
-                        bool ready = true;
+                    if (s0 < n_ranks)
+                        for (;;) {
+                            bool ready = true;
 #pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            if (s0 + j < n_ranks) v[j] = ld_tagged(w0 + (size_t)(s0 + j) * kGsumLen * 2);
+                            for (int j = 0; j < 8; ++j)
+                                if (s0 + j < n_ranks) v[j] = ld_tagged(w0 + (size_t)(s0 + j) * kGsumLen * 2);
 #pragma unroll
-                        for (int j = 0; j < 8; ++j)
-                            if (s0 + j < n_ranks) ready = ready && v[j].y == step_id && v[j].w == step_id;
-                        if (ready) break;
-                        if (++spins > (1u << 22) || (((spins & 255u) == 0u) && ld_acquire_u32(abort_flag) != 0u)) {
-                            atomicExch(abort_flag, 1u);
-                            s_peer_ok = 0;
-                            break;
+                            for (int j = 0; j < 8; ++j)
+                                if (s0 + j < n_ranks) ready = ready && v[j].y == step_id && v[j].w == step_id;
+                            if (ready) break;
+                            if (((++spins & 255u) == 0u) && (poll_expired(t_start) || ld_acquire_u32(abort_flag) != 0u)) {
+                                atomicExch(abort_flag, 1u);
+                                s_peer_ok = 0;
+                                break;
+                            }
                         }
-                    }
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        if (s0 + j < n_ranks) t += __hiloint2double((int)v[j].z, (int)v[j].x);       // rank order: same bits on every GPU
+                    for (int j = 0; j < 8; ++j) rk[s0 + j] = s0 + j < n_ranks ? __hiloint2double((int)v[j].z, (int)v[j].x) : 0.0;
                 }
-                s_g[qq] = t;
+                s_g[qq] = tree_sum<kPeerMaxWorld>(rk, n_ranks);                // pairwise in rank order: same bits on every GPU, and
+                                                                               // the continuation of the ranks' own segment trees
             }
             __syncthreads();
             ORP_TRACE(5);
@@ -1224,7 +1306,7 @@ static int fit_blocks(uint64_t count, int unroll) {
     uint64_t want = (count + tile - 1) / tile;
     if (want < 1) want = 1;
     uint64_t cap = (uint64_t)sm_count();           // 256 threads x ~200 registers: one block per SM
-    if (cap > 512) cap = 512;
+    if (cap > (uint64_t)kLLBlocks) cap = kLLBlocks;
     return (int)(want < cap ? want : cap);
 }
 
@@ -1239,7 +1321,13 @@ static int make_args(const orp_fit_batch* b, FitArgs& a, bool need_target) {
     a.s_t = b->d_s_t; a.s_t1 = b->d_s_t1; a.feat1 = b->d_feat1; a.feat2 = b->d_feat2; a.target = b->d_target;
     a.count = b->count; a.inv_scale = b->inv_scale; a.inv_scale_f = (float)b->inv_scale;
     a.b_t = (float)(b->bond_t * b->inv_scale); a.b_t1 = (float)(b->bond_t1 * b->inv_scale);
+    ORP_REQUIRE(b->paths_dtype == ORP_F64 || b->inv_scale == 1.0,
+                "fp32 price columns must be in network units already (inv_scale = 1): convert with orp_fit_scale_column");
     a.skip = (b->reserved & ORP_FIT_SKIP_NONFINITE) ? 1 : 0;
+    a.n_seg = b->n_seg ? (int)b->n_seg : 1;
+    a.seg_stride = b->seg_stride;
+    ORP_REQUIRE(a.n_seg >= 1 && a.n_seg <= ORP_FIT_MAX_SEGMENTS, "n_seg must be in [1, %d]", ORP_FIT_MAX_SEGMENTS);
+    ORP_REQUIRE(a.n_seg == 1 || a.seg_stride >= a.count, "seg_stride must be >= count (segments may not overlap)");
     return ORP_OK;
 }
 
@@ -1280,7 +1368,7 @@ extern "C" int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const
 #undef CALL_GRAD
 #undef CALL_GRAD_SKIP
     ORP_LAUNCH_CHECK("fit_grad_kernel");
-    fit_reduce_kernel<<<1, 256, 0, st>>>(partials, grid, d_state, d_gsum);
+    fit_reduce_kernel<<<1, 256, 0, st>>>(partials, grid, a.n_seg, d_state, d_gsum);
     ORP_LAUNCH_CHECK("fit_reduce_kernel");
     return ORP_OK;
 }
@@ -1438,6 +1526,7 @@ extern "C" int orp_fit_predict(const orp_fit_batch* b, const float* d_params, fl
     int rc = make_args(b, a, false);
     if (rc) return rc;
     ORP_REQUIRE(d_params && d_sums && d_scratch, "null pointer");
+    ORP_REQUIRE(a.n_seg == 1, "orp_fit_predict takes one segment per call");
     cudaStream_t st = (cudaStream_t)stream;
     uint64_t want = (a.count + kFitThreads - 1) / kFitThreads;
     // four resident blocks per SM (launch bounds), a whole number of waves: 592 blocks on B200, not 512 (3.46 per SM);
@@ -1465,6 +1554,7 @@ extern "C" int orp_fit_residuals(const orp_fit_batch* b, const float* d_params, 
     int rc = make_args(b, a, true);
     if (rc) return rc;
     ORP_REQUIRE(d_params && d_resid_out, "null pointer");
+    ORP_REQUIRE(a.n_seg == 1, "orp_fit_residuals takes one segment per call");
     cudaStream_t st = (cudaStream_t)stream;
     uint64_t want = (a.count + kFitThreads - 1) / kFitThreads;
     const uint64_t cap = 4ull * (uint64_t)sm_count();          // four resident blocks per SM, whole waves
@@ -1488,11 +1578,35 @@ extern "C" int orp_fit_epoch_minibatch(const orp_fit_batch* b, float* d_params, 
     if (rc) return rc;
     ORP_REQUIRE(d_params && d_state, "null pointer");
     ORP_REQUIRE(batch_size >= 1, "batch_size must be >= 1");
+    ORP_REQUIRE(a.n_seg == 1, "the mini-batch driver takes one segment");
     ORP_REQUIRE(!a.skip, "ORP_FIT_SKIP_NONFINITE is not available in the Keras-faithful mini-batch driver");
     cudaStream_t st = (cudaStream_t)stream;
 #define CALL_MINI(NET, LOSS, T) fit_minibatch_kernel<NET, LOSS, T><<<1, kMiniThreads, 0, st>>>(a, d_params, d_state, batch_size, epoch_seed)
     ORP_FIT_DISPATCH(CALL_MINI);
 #undef CALL_MINI
     ORP_LAUNCH_CHECK("fit_minibatch_kernel");
+    return ORP_OK;
+}
+
+// ---- price column in network units: (float)((double)S * inv_scale), the cast Keras applies to its inputs ----------
+namespace orp {
+template <typename T>
+__global__ void __launch_bounds__(256) scale_column_kernel(const T* __restrict__ in, uint64_t n, double inv_scale, float* __restrict__ out) {
+    for (uint64_t i = (uint64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (uint64_t)gridDim.x * 256)
+        out[i] = (float)((double)in[i] * inv_scale);
+}
+}  // namespace orp
+
+extern "C" int orp_fit_scale_column(const void* d_in, int dtype, uint64_t count, double inv_scale, float* d_out, void* stream) {
+    ORP_REQUIRE(d_in && d_out, "null pointer");
+    ORP_REQUIRE(dtype == ORP_F64 || dtype == ORP_F32, "dtype must be ORP_F64 or ORP_F32");
+    if (count == 0) return ORP_OK;
+    uint64_t want = (count + 255) / 256;
+    const uint64_t cap = 8ull * (uint64_t)sm_count();
+    const int grid = (int)(want < cap ? want : cap);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == ORP_F64) scale_column_kernel<double><<<grid, 256, 0, st>>>(reinterpret_cast<const double*>(d_in), count, inv_scale, d_out);
+    else scale_column_kernel<float><<<grid, 256, 0, st>>>(reinterpret_cast<const float*>(d_in), count, inv_scale, d_out);
+    ORP_LAUNCH_CHECK("scale_column_kernel");
     return ORP_OK;
 }

@@ -23,6 +23,7 @@ F64, F32 = 0, 1
 MAX_OPTIONS = 64
 FIT_MAX_PARAMS = 128
 FIT_STATE_DOUBLES = 1024
+FIT_MAX_SEGMENTS = 8
 GSUM_LEN = FIT_MAX_PARAMS + 2
 
 # indices into the device-resident fit state (mirror of the enum in csrc/orp_fit.cu)
@@ -46,7 +47,8 @@ class FitBatch(C.Structure):
     _fields_ = [("net", C.c_int32), ("loss", C.c_int32), ("paths_dtype", C.c_int32), ("reserved", C.c_int32),
                 ("count", C.c_uint64), ("d_s_t", C.c_void_p), ("d_s_t1", C.c_void_p),
                 ("d_feat1", C.c_void_p), ("d_feat2", C.c_void_p), ("d_target", C.c_void_p),
-                ("inv_scale", C.c_double), ("bond_t", C.c_double), ("bond_t1", C.c_double)]
+                ("inv_scale", C.c_double), ("bond_t", C.c_double), ("bond_t1", C.c_double),
+                ("n_seg", C.c_uint32), ("reserved2", C.c_uint32), ("seg_stride", C.c_uint64)]
 
 
 _vp, _u64, _i32, _f64 = C.c_void_p, C.c_uint64, C.c_int, C.c_double
@@ -79,6 +81,7 @@ PROTOTYPES = {
     "orp_peer_buffer_open": (C.c_int, [_vp, C.POINTER(C.c_void_p)]),
     "orp_peer_buffer_close": (C.c_int, [_vp]),
     "orp_peer_buffer_destroy": (C.c_int, [_vp]),
+    "orp_fit_scale_column": (C.c_int, [_vp, _i32, _u64, _f64, _vp, _vp]),
     "orp_fit_begin": (C.c_int, [_vp, _i32, _i32, _i32, _vp]),
     "orp_fit_init": (C.c_int, [_vp, _vp]),
     "orp_fit_end": (C.c_int, [_i32, _vp, _vp, _vp]),

@@ -20,7 +20,7 @@ import numpy as np
 from . import _lib
 import os
 
-from .dist import allreduce_sum_, is_distributed, rank_world
+from .dist import allgather_rows, allgather_tree_sum_, allreduce_sum_, is_distributed, rank_world, tree_sum_rows
 
 HIDDEN = 8
 NET_IO = {"eo": (1, 1), "rp": (3, 2)}
@@ -41,6 +41,20 @@ def init_params(net: str, seed: int, out_bias) -> np.ndarray:
     w3 = rng.normal(0.0, 0.1, size=(HIDDEN, o))
     b3 = np.broadcast_to(np.asarray(out_bias, dtype=np.float64), (o,))
     return np.concatenate([w1.ravel(), np.zeros(HIDDEN), w2.ravel(), np.zeros(HIDDEN), w3.ravel(), b3]).astype(np.float32)
+
+
+def scale_column(col, inv_scale: float, out=None):
+    """``(float)((double) col * inv_scale)`` on the device: a price column in network units (EO cell 13 divides by
+    ``ADJUSTMENT_FACTOR``; Keras casts to fp32).  The fit kernels read such fp32 columns as they are."""
+    torch = _lib.require_cuda()
+    if not col.is_contiguous():
+        raise ValueError("columns must be contiguous (use the time-major path tensor)")
+    if out is None:
+        out = torch.empty(col.shape, dtype=torch.float32, device=col.device)
+    with torch.cuda.device(col.device):
+        _lib.check(_lib.lib().orp_fit_scale_column(_lib.ptr(col), _lib.F64 if col.dtype == torch.float64 else _lib.F32,
+                                                   col.numel(), float(inv_scale), _lib.ptr(out), _lib.stream_ptr()))
+    return out
 
 
 def _nccl_group(group) -> bool:
@@ -85,7 +99,7 @@ class ReplicationNet:
         self.gsum = torch.zeros(_lib.GSUM_LEN, dtype=torch.float64, device=self.device)
         # zero-filled: the persistent kernel's hand-offs are tagged with a step counter kept in this buffer
         self.scratch = torch.zeros(_lib.lib().orp_fit_scratch_bytes(), dtype=torch.uint8, device=self.device)
-        self.sums = torch.zeros(5, dtype=torch.float64, device=self.device)
+        self.sums = torch.zeros((1, 5), dtype=torch.float64, device=self.device)
         self.launches = 0
         self.two_stage = False      # True forces grad -> [all-reduce] -> update even on one GPU (tests, multi-GPU form)
         self.persistent = True      # False: one launch per optimiser step (orp_fit_epochs) instead of one per fit
@@ -155,16 +169,27 @@ class ReplicationNet:
         return self._equal_counts[count]
 
     def batch(self, s_t, s_t1, target, inv_scale, bond_t, bond_t1, loss="mse", feat1=None, feat2=None,
-              skip_nonfinite: bool = False):
+              skip_nonfinite: bool = False, segments: int = 1):
+        """One time step's inputs as the C struct.  fp32 price columns that are not in network units yet
+        (``inv_scale != 1``) are converted once here (``scale_column``), because the kernels take fp32 columns as they
+        are.  ``segments``: the arrays are cut into that many equally long pieces that are reduced separately and
+        added pairwise (``orp_fit_batch.n_seg``: the virtual shards that make the sums rank-count invariant)."""
         torch = _lib.require_cuda()
+        for t in (s_t, s_t1, target, feat1, feat2):
+            if t is not None and not t.is_contiguous():
+                raise ValueError("columns must be contiguous (use the time-major path tensor)")
+        if s_t.dtype != torch.float64 and float(inv_scale) != 1.0:
+            s_t, s_t1 = scale_column(s_t, inv_scale), scale_column(s_t1, inv_scale)
+            bond_t, bond_t1, inv_scale = bond_t * float(inv_scale), bond_t1 * float(inv_scale), 1.0
+        n, L = s_t.numel(), int(segments)
+        if L < 1 or L > _lib.FIT_MAX_SEGMENTS or n % L:
+            raise ValueError(f"segments must be in [1, {_lib.FIT_MAX_SEGMENTS}] and divide the path count")
         b = _lib.FitBatch()
         b.net, b.loss = _lib.NET[self.net], _lib.LOSS[loss]
         b.paths_dtype = _lib.F64 if s_t.dtype == torch.float64 else _lib.F32
         b.reserved = 1 if skip_nonfinite else 0          # ORP_FIT_SKIP_NONFINITE
-        b.count = s_t.numel()
-        for t in (s_t, s_t1, target, feat1, feat2):
-            if t is not None and not t.is_contiguous():
-                raise ValueError("columns must be contiguous (use the time-major path tensor)")
+        b.count = n // L
+        b.n_seg, b.seg_stride = L, n // L
         b.d_s_t, b.d_s_t1 = _lib.ptr(s_t), _lib.ptr(s_t1)
         b.d_feat1, b.d_feat2, b.d_target = _lib.ptr(feat1) or None, _lib.ptr(feat2) or None, _lib.ptr(target) or None
         b.inv_scale, b.bond_t, b.bond_t1 = float(inv_scale), float(bond_t), float(bond_t1)
@@ -173,27 +198,30 @@ class ReplicationNet:
         return b
 
     @staticmethod
+    def _offset(b, off: int, count: int, n_seg: int):
+        """A copy of ``b`` whose arrays start ``off`` samples later: ``n_seg`` segments of ``count`` samples."""
+        c = _lib.FitBatch()
+        C.memmove(C.byref(c), C.byref(b), C.sizeof(_lib.FitBatch))
+        c.count, c.n_seg = count, n_seg
+        c.d_s_t, c.d_s_t1 = b.d_s_t + off * b._esz, b.d_s_t1 + off * b._esz
+        c.d_target = b.d_target + off * 4 if b.d_target else None
+        c.d_feat1 = b.d_feat1 + off * 4 if b.d_feat1 else None
+        c.d_feat2 = b.d_feat2 + off * 4 if b.d_feat2 else None
+        c._keep, c._esz = b._keep, b._esz
+        return c
+
+    @staticmethod
     def split(b, steps_per_epoch: int):
-        """The batch cut into ``steps_per_epoch`` contiguous index ranges (Keras' ``batch_size`` =
-        ``count / steps_per_epoch``).  Contiguous blocks of a Sobol sequence are themselves well stratified,
-        so no shuffle is needed; on several GPUs batch ``k`` is the union of every rank's ``k``-th range."""
+        """The batch cut into ``steps_per_epoch`` optimiser steps (Keras' ``batch_size`` = ``count / steps_per_epoch``):
+        step ``k`` takes the ``k``-th contiguous range of EVERY segment.  Contiguous blocks of a Sobol sequence are
+        themselves well stratified, so no shuffle is needed; on several GPUs step ``k`` is the union of the ``k``-th
+        ranges of all virtual shards, whichever rank holds them."""
         n = int(b.count)
         k = max(1, min(int(steps_per_epoch), n))
         if k == 1:
             return [b]
         per = -(-n // k)
-        out = []
-        for off in range(0, n, per):
-            c = _lib.FitBatch()
-            C.memmove(C.byref(c), C.byref(b), C.sizeof(_lib.FitBatch))
-            c.count = min(per, n - off)
-            c.d_s_t, c.d_s_t1 = b.d_s_t + off * b._esz, b.d_s_t1 + off * b._esz
-            c.d_target = b.d_target + off * 4 if b.d_target else None
-            c.d_feat1 = b.d_feat1 + off * 4 if b.d_feat1 else None
-            c.d_feat2 = b.d_feat2 + off * 4 if b.d_feat2 else None
-            c._keep = b._keep
-            out.append(c)
-        return out
+        return [ReplicationNet._offset(b, off, min(per, n - off), int(b.n_seg) or 1) for off in range(0, n, per)]
 
     def fit(self, batch, opt: Optimizer, epochs: int, patience: int, use_schedule: bool, mode: str = "scaled",
             batch_size: int = 512, shuffle_seed: int = 0, check_every: int = 16, steps_per_epoch: int = 1):
@@ -246,7 +274,7 @@ class ReplicationNet:
                             _lib.check(L.orp_fit_grad(C.byref(part), _lib.ptr(self.params), _lib.ptr(opt.state),
                                                       _lib.ptr(self.gsum), _lib.ptr(self.scratch), st))
                             if dist_on:
-                                allreduce_sum_(self.gsum, self.group)
+                                allgather_tree_sum_(self.gsum, self.group)     # pairwise in rank order, as the peer exchange adds
                             flags = (1 if k == 0 else 0) | (2 if k == len(parts) - 1 else 0)
                             _lib.check(L.orp_fit_update(netc, _lib.ptr(self.params), _lib.ptr(opt.state),
                                                         _lib.ptr(self.gsum), flags, st))
@@ -275,21 +303,45 @@ class ReplicationNet:
         """``out[i] = target_i - V(X1)_i`` with the current weights: the reference's per-path ``VaR`` array
         (``get_phi_psi_VaR``, ``Replicating_Portfolio.py:120``), kept on the device."""
         torch = _lib.require_cuda()
+        L, n = int(batch.n_seg) or 1, int(batch.count)
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().orp_fit_residuals(C.byref(batch), _lib.ptr(self.params), _lib.ptr(out), _lib.stream_ptr()))
-            self.launches += 1
+            for v in range(L):
+                seg = self._offset(batch, v * int(batch.seg_stride), n, 1) if L > 1 else batch
+                _lib.check(_lib.lib().orp_fit_residuals(C.byref(seg), _lib.ptr(self.params), _lib.ptr(out) + 4 * v * int(batch.seg_stride),
+                                                        _lib.stream_ptr()))
+                self.launches += 1
         return out
 
     def predict(self, batch, values_out=None):
         """``model.predict(X0)`` into ``values_out`` (fp32) and the global sums
-        ``(sum V, sum phi, sum psi, sum |y - V(X1)|, sum |y - V(X1)| / max(|y|, 1e-7))`` as a 5-vector on the host."""
+        ``(sum V, sum phi, sum psi, sum |y - V(X1)|, sum |y - V(X1)| / max(|y|, 1e-7))`` as a 5-vector on the host.
+        One kernel pass per segment; the segments' sums of all ranks are added pairwise in global segment order on the
+        host, so the result does not depend on the number of ranks that hold the virtual shards."""
         torch = _lib.require_cuda()
+        L, n = int(batch.n_seg) or 1, int(batch.count)
+        if self.sums.shape[0] != L:
+            self.sums = torch.zeros((L, 5), dtype=torch.float64, device=self.device)
         with torch.cuda.device(self.device):
-            _lib.check(_lib.lib().orp_fit_predict(C.byref(batch), _lib.ptr(self.params), _lib.ptr(values_out),
-                                                  _lib.ptr(self.sums), _lib.ptr(self.scratch), _lib.stream_ptr()))
-            self.launches += 2
-            allreduce_sum_(self.sums, self.group)
-            return self.sums.cpu().numpy().copy()
+            for v in range(L):
+                seg = self._offset(batch, v * int(batch.seg_stride), n, 1) if L > 1 else batch
+                vo = _lib.ptr(values_out) + 4 * v * int(batch.seg_stride) if values_out is not None else 0
+                _lib.check(_lib.lib().orp_fit_predict(C.byref(seg), _lib.ptr(self.params), vo, _lib.ptr(self.sums[v]),
+                                                      _lib.ptr(self.scratch), _lib.stream_ptr()))
+                self.launches += 2
+            rows = allgather_rows(self.sums, self.group)             # (world, L, 5): global segment v = rank * L + local
+            return tree_sum_rows(rows.reshape(-1, 5))
+
+
+def virtual_segments(count: int, group=None, virtual_shards: int = 8) -> int:
+    """How many of the ``virtual_shards`` equal pieces of the GLOBAL path range this rank holds: ``virtual_shards /
+    world`` when that is a whole number and divides the local path count (world = 1, 2, 4, 8 for the default 8), else
+    1 (the sums are then still deterministic, but depend on the world size)."""
+    _, world = rank_world(group)
+    if virtual_shards >= world and virtual_shards % world == 0:
+        L = virtual_shards // world
+        if L <= _lib.FIT_MAX_SEGMENTS and count % L == 0 and count >= L:
+            return L
+    return 1
 
 
 def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: str = "scaled", scale: float = 1.0,
@@ -297,7 +349,8 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
                     epochs_first: int = 500, epochs_next: int = 100, patience_first: int = 50, patience_next: int = 7,
                     batch_size: int = 512, shuffle_seed: int = 0, features=None, second_model: bool = False,
                     cost_of_capital: float = 0.1, check_every: int = 16, verbose: bool = False, on_step=None,
-                    steps_per_epoch: int = 8, var_quantiles=None, on_step_end=None, skip_nonfinite: bool = False):
+                    steps_per_epoch: int = 8, var_quantiles=None, on_step_end=None, skip_nonfinite: bool = False,
+                    virtual_shards: int | None = None):
     """Backward replication over all kept columns.
 
     ``paths_tm``: TIME-MAJOR ``(n_cols, count)`` CUDA tensor of this rank's paths; ``bond``: ``n_cols`` bond
@@ -317,6 +370,15 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
     take no part in the fits, keep NaN as their value and stay out of the means and quantiles — without it one such
     path turns every weight into NaN, exactly as in the reference.
 
+    ``virtual_shards`` (scaled mode): the global path range is treated as that many equal pieces; every optimiser step,
+    predict sum and mean is formed per piece and the pieces are added pairwise in index order, so ``V0``, the hedge
+    weights and the fitted parameters are bit-identical on 1, 2, 4 or 8 GPUs (``virtual_segments``).  Default: 8 from
+    2^18 paths (all ranks together) on, 1 below.  The price of the invariance is the make-up of an optimiser step: step
+    ``k`` is the ``k``-th range of every shard instead of one contiguous index range, i.e. 8 aligned Sobol blocks of 1/64
+    of the paths instead of one block of 1/8 — immaterial for large sets (2^20 paths: 8 x 16384-point nets per step),
+    but at the reference's 4096 paths it would replace a 512-point net by 8 clustered 64-point nets and visibly raise
+    the gradient noise, so small runs keep the contiguous batches.
+
     Returns ``dict(V0, phi0, psi0, steps=[...], launches)`` in network units."""
     torch = _lib.require_cuda()
     n_cols, count = paths_tm.shape
@@ -324,33 +386,52 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
     bond = np.asarray(bond, dtype=np.float64)
     if bond.shape != (n_cols,):
         raise ValueError("bond must have one entry per kept column")
-    if skip_nonfinite:
-        t_fin = torch.isfinite(terminal_values) & torch.isfinite(paths_tm[-1])     # e.g. -inf price, payoff 0
-        t_sum, t_cnt = terminal_values.double()[t_fin].sum(), int(t_fin.sum())
-    else:
-        t_sum, t_cnt = terminal_values.double().sum(), count
-    tot = torch.tensor([float(t_cnt), float(t_sum)], dtype=torch.float64, device=device)
-    allreduce_sum_(tot, group)
-    tot = tot.cpu().numpy()
+    if virtual_shards is None:
+        if total_paths is None:
+            cnt = torch.tensor([float(count)], dtype=torch.float64, device=device)
+            n_global = float(allreduce_sum_(cnt, group))
+        else:
+            n_global = float(total_paths)
+        virtual_shards = 8 if n_global >= 2 ** 18 else 1
+    L = virtual_segments(count, group, int(virtual_shards)) if mode == "scaled" else 1
+    seg = count // L
+    tv = terminal_values.contiguous()
+    rows = torch.zeros((L, 2), dtype=torch.float64, device=device)      # per virtual shard: (paths that count, sum of targets)
+    for v in range(L):
+        piece = tv[v * seg:(v + 1) * seg].double()
+        if skip_nonfinite:
+            fin = torch.isfinite(piece) & torch.isfinite(paths_tm[-1, v * seg:(v + 1) * seg])     # e.g. -inf price, payoff 0
+            rows[v, 0], rows[v, 1] = fin.sum(), piece[fin].sum()
+        else:
+            rows[v, 0], rows[v, 1] = float(seg), piece.sum()
+    tot = tree_sum_rows(allgather_rows(rows, group).reshape(-1, 2))    # pairwise over the global shards: rank-count invariant
     total = float(tot[0]) if total_paths is None else float(total_paths)
     if out_bias is None:
         out_bias = tot[1] / total                      # EO cell 12: payoff.mean() / ADJUSTMENT_FACTOR
     model = ReplicationNet(net, init_params(net, init_seed, out_bias), device, group)
     opt1 = Optimizer(device)
     opt2 = Optimizer(device) if second_model else None
-    v_next = terminal_values.contiguous()
+    v_next = tv
     v_cur = torch.empty_like(v_next)
     h_buf = torch.empty_like(v_next) if second_model else None
     steps, first = [], True
     resid_buf = None
     phi0 = psi0 = v0 = float("nan")
+    # Price columns in network units, fp32, converted ONCE per time step (column t+1 of this step is column t of the
+    # previous one): the epoch loop then reads 12 bytes per sample and does no fp64 arithmetic.  Same bits as the
+    # kernels' own conversion of the fp64 columns.
+    inv = 1.0 / scale
+    x_next = scale_column(paths_tm[n_cols - 1], inv)
+    x_cur = torch.empty_like(x_next)
     for t_i in range(n_cols - 2, -1, -1):
         if on_step is not None:
             on_step({"t_i": t_i})
         f1, f2 = features(t_i) if features is not None else (None, None)
-        common = dict(inv_scale=1.0 / scale, bond_t=bond[t_i], bond_t1=bond[t_i + 1], feat1=f1, feat2=f2,
-                      skip_nonfinite=skip_nonfinite)
-        b = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="mse", **common)
+        scale_column(paths_tm[t_i], inv, out=x_cur)
+        common = dict(inv_scale=1.0, bond_t=bond[t_i] * inv, bond_t1=bond[t_i + 1] * inv, feat1=f1, feat2=f2,
+                      skip_nonfinite=skip_nonfinite, segments=L)
+        model.launches += 1
+        b = model.batch(x_cur, x_next, v_next, loss="mse", **common)
         h = model.fit(b, opt1, epochs_first if first else epochs_next, patience_first if first else patience_next,
                       use_schedule=first, mode=mode, batch_size=batch_size,
                       shuffle_seed=shuffle_seed * 4096 + 2 * t_i, check_every=check_every, steps_per_epoch=steps_per_epoch)
@@ -363,7 +444,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
                    mean_V=sums[0] / total, phi=sums[1] / total, psi=sums[2] / total, mae=sums[3] / total,
                    mape=100.0 * sums[4] / total)       # Keras 'mae' / 'mape' of model1.evaluate(X1, ...), RP.py:215
         if second_model:
-            b2 = model.batch(paths_tm[t_i], paths_tm[t_i + 1], v_next, loss="pinball", **common)
+            b2 = model.batch(x_cur, x_next, v_next, loss="pinball", **common)
             h2 = model.fit(b2, opt2, epochs_first if first else epochs_next, patience_first if first else patience_next,
                            use_schedule=first, mode=mode, batch_size=batch_size,
                            shuffle_seed=shuffle_seed * 4096 + 2 * t_i + 1, check_every=check_every,
@@ -385,6 +466,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
         if verbose:
             print(rec)
         v_next, v_cur = v_cur, v_next
+        x_next, x_cur = x_cur, x_next
         phi0, psi0, v0 = rec["phi"], rec["psi"], rec["mean_V"]
         first = False
     out = {"V0": v0, "phi0": phi0, "psi0": psi0, "steps": steps, "launches": model.launches,

@@ -33,7 +33,7 @@ def test_library_exports_every_declared_symbol():
 def test_struct_layouts_match_header():
     from orp_b200 import _lib
     assert ctypes.sizeof(_lib.PathParams) == 6 * 4 + 8 * 8
-    assert ctypes.sizeof(_lib.FitBatch) == 4 * 4 + 8 + 5 * 8 + 3 * 8
+    assert ctypes.sizeof(_lib.FitBatch) == 4 * 4 + 8 + 5 * 8 + 3 * 8 + 2 * 4 + 8
     assert _lib.lib().orp_fit_n_params(0) == 97 and _lib.lib().orp_fit_n_params(1) == 122   # Keras summaries
     assert _lib.lib().orp_version() >= 100
 

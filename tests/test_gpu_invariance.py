@@ -1,0 +1,156 @@
+"""Rank-count invariance of the fit (SURVEY.md section 7 hard part 7, section 4 test 5): the fitted weights, the losses and
+the predict sums must not depend on how many GPUs share the paths.
+
+The paths are cut into 8 virtual shards of the global index space; a world of W ranks gives each rank 8 / W of them as
+the segments of its batches (``orp_fit_batch.n_seg``).  Worlds of 2, 4 and 8 ranks are emulated here on ONE GPU through
+the generic two-stage form (``orp_fit_grad`` per rank on that rank's slice of the arrays -> pairwise sum over ranks ->
+``orp_fit_update``), which is what N processes with any collective library would run; the results are compared BIT FOR
+BIT with the single-GPU drivers (persistent kernel and two-stage) holding all 8 shards.  (Kernels that wait on each
+other are never run as separate launches on one GPU; the real multi-process runs are in test_gpu_multi.py.)"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+V = 8
+
+
+def _data(n, seed, net):
+    rng = np.random.default_rng(seed)
+    s_t = 100.0 * np.exp(0.2 * rng.standard_normal(n))
+    s_t1 = s_t * np.exp(0.03 * rng.standard_normal(n))
+    y = (np.maximum(s_t1 - 100.0, 0) / 100.0).astype(np.float32)
+    f1 = (1.0 - 0.01 * rng.random(n)).astype(np.float32)
+    f2 = (0.01 + 0.001 * rng.standard_normal(n)).astype(np.float32)
+    return s_t, s_t1, y, (f1 if net == "rp" else None), (f2 if net == "rp" else None)
+
+
+def _tree(ts):
+    ts, stride = list(ts), 1
+    while stride < len(ts):
+        for i in range(0, len(ts) - stride, 2 * stride):
+            ts[i] = ts[i] + ts[i + stride]
+        stride *= 2
+    return ts[0]
+
+
+def _emulated_world(W, net, data, p0, cuda, fits, spe, loss="mse"):
+    """W ranks on one GPU: rank r owns the contiguous slice r of the arrays (8 / W virtual shards)."""
+    from orp_b200 import _lib
+    from orp_b200.fit import ReplicationNet, Optimizer
+    L_ = _lib.lib()
+    st = _lib.stream_ptr()
+    dev = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a)).to(cuda)
+    n = data[0].size
+    per = n // W
+    model = ReplicationNet(net, p0, cuda)
+    opt = Optimizer(cuda)
+    ranks = []
+    for r in range(W):
+        sl = slice(r * per, (r + 1) * per)
+        arrs = [dev(a[sl]) if a is not None else None for a in data]
+        b = model.batch(arrs[0], arrs[1], arrs[2], 1 / 100.0, 1.02, 1.03, loss=loss, feat1=arrs[3], feat2=arrs[4], segments=V // W)
+        ranks.append((b, model.split(b, spe), torch.zeros(_lib.GSUM_LEN, dtype=torch.float64, device=cuda)))
+    hist = []
+    for epochs, patience, sched in fits:
+        _lib.check(L_.orp_fit_begin(_lib.ptr(opt.state), epochs, patience, int(sched), st))
+        for _ in range(epochs):
+            for k in range(len(ranks[0][1])):
+                for b, parts, g in ranks:
+                    _lib.check(L_.orp_fit_grad(C.byref(parts[k]), _lib.ptr(model.params), _lib.ptr(opt.state), _lib.ptr(g),
+                                               _lib.ptr(model.scratch), st))
+                total = _tree([g.clone() for _, _, g in ranks])
+                flags = (1 if k == 0 else 0) | (2 if k == len(ranks[0][1]) - 1 else 0)
+                _lib.check(L_.orp_fit_update(_lib.NET[net], _lib.ptr(model.params), _lib.ptr(opt.state), _lib.ptr(total), flags, st))
+        _lib.check(L_.orp_fit_end(_lib.NET[net], _lib.ptr(model.params), _lib.ptr(opt.state), st))
+        hist.append(opt.head()[:14].copy())
+    # predict sums: per rank and segment, then pairwise in global segment order
+    rows = []
+    for b, _, _ in ranks:
+        model.group = None
+        model.predict(b, None)
+        rows.append(model.sums.cpu().numpy().copy())
+    from orp_b200.dist import tree_sum_rows
+    sums = tree_sum_rows(np.concatenate(rows).reshape(-1, 5))
+    return model.params.cpu().numpy().copy(), opt.state[:400].cpu().numpy().copy(), hist, sums
+
+
+@pytest.mark.parametrize("net,seg_len,spe", [("eo", 40_000, 4), ("eo", 5_001, 3), ("rp", 3_000, 2)])
+def test_fit_is_bit_identical_for_worlds_of_1_2_4_8(cuda, net, seg_len, spe):
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    n = V * seg_len
+    data = _data(n, 11, net)
+    p0 = init_params(net, 1234, 0.1 if net == "eo" else [0.9, 0.1])
+    fits = [(12, 50, True), (5, 2, False)]
+    dev = lambda a: None if a is None else torch.from_numpy(a).to(cuda)
+    ref = {}
+    for persistent, two_stage in ((True, False), (False, True), (False, False)):
+        model = ReplicationNet(net, p0, cuda)
+        model.persistent, model.two_stage = persistent, two_stage
+        opt = Optimizer(cuda)
+        b = model.batch(dev(data[0]), dev(data[1]), dev(data[2]), 1 / 100.0, 1.02, 1.03, feat1=dev(data[3]), feat2=dev(data[4]),
+                        segments=V)
+        hist = []
+        for epochs, patience, sched in fits:
+            model.fit(b, opt, epochs, patience, sched, mode="scaled", steps_per_epoch=spe)
+            hist.append(opt.head()[:14].copy())
+        sums = model.predict(b, None)
+        ref[(persistent, two_stage)] = (model.params.cpu().numpy().copy(), opt.state[:400].cpu().numpy().copy(), hist, sums)
+        model.close()
+    base = ref[(True, False)]
+    for key, got in ref.items():
+        assert np.array_equal(got[0], base[0]) and np.array_equal(got[1], base[1]), key
+    assert np.isfinite(base[0]).all() and base[2][0][10] > 0                      # a real fit: finite weights, a loss
+    for W in (2, 4, 8):
+        w, state, hist, sums = _emulated_world(W, net, data, p0, cuda, fits, spe)
+        assert np.array_equal(w, base[0]), f"weights differ at world {W}"
+        assert np.array_equal(state, base[1]), f"optimiser state differs at world {W}"
+        assert all(np.array_equal(a, b) for a, b in zip(hist, base[2]))
+        assert np.array_equal(sums, base[3]), f"predict sums differ at world {W}"
+
+
+def test_one_segment_differs_only_by_summation_order(cuda):
+    """Sanity of the comparison itself: the same batch as ONE segment is another association of the same sums — close
+    (1e-6 of the gradient's max-norm) but in general not the same bits."""
+    from orp_b200 import _lib
+    from orp_b200.fit import ReplicationNet, Optimizer, init_params
+    n = V * 20_000
+    data = _data(n, 5, "eo")
+    p0 = init_params("eo", 7, 0.1) + np.random.default_rng(3).normal(0, 0.2, 97).astype(np.float32)
+    dev = lambda a: torch.from_numpy(a).to(cuda)
+    g = []
+    for segments in (1, V):
+        model = ReplicationNet("eo", p0, cuda)
+        opt = Optimizer(cuda)
+        b = model.batch(dev(data[0]), dev(data[1]), dev(data[2]), 1 / 100.0, 1.02, 1.03, segments=segments)
+        _lib.check(_lib.lib().orp_fit_begin(_lib.ptr(opt.state), 5, 5, 0, _lib.stream_ptr()))
+        _lib.check(_lib.lib().orp_fit_grad(C.byref(b), _lib.ptr(model.params), _lib.ptr(opt.state), _lib.ptr(model.gsum),
+                                           _lib.ptr(model.scratch), _lib.stream_ptr()))
+        g.append(model.gsum.cpu().numpy().copy())
+    assert g[0][_lib.FIT_MAX_PARAMS + 1] == g[1][_lib.FIT_MAX_PARAMS + 1] == n
+    np.testing.assert_allclose(g[0], g[1], rtol=0, atol=1e-6 * np.abs(g[1][:97]).max() * 1.0 + 1e-6 * abs(g[1][128]))
+
+
+def test_backward_replication_uses_the_virtual_shards(cuda):
+    """fit_replication: from 2^18 paths on the default is 8 virtual shards (the run equals virtual_shards=8 bit for
+    bit and is another optimiser trajectory than the unsharded batches: close, not equal); small runs keep the
+    contiguous batches of the reference's own batch size (default == virtual_shards=1)."""
+    import orp_b200
+    p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 12)
+    D = 3
+    kw = dict(net="eo", scale=100.0, epochs_first=30, epochs_next=5)
+    out = {}
+    for m in (18, 13):
+        tm = orp_b200.simulate_paths("gbm_log", p, m=m, steps=D, time_major=True)
+        bond = orp_b200.bond_curve(0.05, D / 12, D + 1)
+        vals = torch.empty(2 ** m, dtype=torch.float32, device=cuda)
+        orp_b200.payoff_sums(tm, [100.0], [-1], "call", values_out=vals, value_scale=1 / 100.0)
+        out[m] = [orp_b200.fit_replication(tm, bond, vals.clone(), virtual_shards=vs, **kw) for vs in (None, 8, 1)]
+    a, b, c = out[18]
+    assert a["V0"] == b["V0"] and np.array_equal(a["params"], b["params"])
+    assert not np.array_equal(a["params"], c["params"]) and abs(a["V0"] / c["V0"] - 1) < 0.1
+    a, b, c = out[13]
+    assert a["V0"] == c["V0"] and np.array_equal(a["params"], c["params"])
