@@ -529,14 +529,16 @@ __device__ __forceinline__ uint4 ld_tagged(const double* entry) {
     return make_uint4((unsigned int)e0, (unsigned int)(e0 >> 32), (unsigned int)e1, (unsigned int)(e1 >> 32));   // {low, tag, high, tag}
 }
 
+// Warp totals of one unit's per-thread gradients, loss and sample count -> red[0 .. P + 2) in shared memory (gradient in
+// parameter order, then loss, then count).  No block barrier: the warps of a block drift apart from unit to unit, so one
+// warp's reduction (shuffles and selects) overlaps the other warps' arithmetic.
 template <int NET>
-__device__ __forceinline__ void block_partial(const Grads<NET>& g, float loss, uint32_t n, float (&s_red)[kFitThreads / 32][Net<NET>::P + 2],
-                                              double* __restrict__ dst, size_t stride, unsigned int tag = 0u) {
+__device__ __forceinline__ void warp_partial(const Grads<NET>& g, float loss, uint32_t n, float* __restrict__ red) {
     constexpr int P = Net<NET>::P;
     constexpr int N = P + 2;
     constexpr int NB = (N % 32) <= 4 ? (N / 32) * 32 : ((N + 31) / 32) * 32;      // EO: 96 (+ 3 by the classic tree); RP: 128
     constexpr int REST = N > NB ? N - NB : 0;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
     float a[NB];
 #pragma unroll
     for (int k = 0; k < NB; ++k) a[k] = k < P ? g.get(k) : (k == P ? loss : (k == P + 1 ? (float)n : 0.f));
@@ -544,29 +546,36 @@ __device__ __forceinline__ void block_partial(const Grads<NET>& g, float loss, u
 #pragma unroll
     for (int i = 0; i < NB / 32; ++i) {
         const int q = scattered_index<NB>(i, lane);
-        if (q < N) s_red[warp][q] = a[i];
+        if (q < N) red[q] = a[i];
     }
 #pragma unroll
     for (int k = NB; k < NB + REST; ++k) {
         float v = k < P ? g.get(k) : (k == P ? loss : (float)n);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
-        if (lane == 0) s_red[warp][k] = v;
-    }
-    __syncthreads();
-    for (int q = threadIdx.x; q < N; q += kFitThreads) {
-        double t = 0.0;
-#pragma unroll
-        for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[w][q];
-        const size_t at = (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * stride;
-        if (tag) st_tagged(dst + 2 * at, t, tag); else dst[at] = t;
+        if (lane == 0) red[k] = v;
     }
 }
 
+// Block totals of the n_seg units of a step as fp64 vectors: for every (segment, column) the warps' totals are added in
+// warp order and written to dst[(segment * seg_stride + index * stride)] (index = k for the gradient of parameter k,
+// ORP_FIT_MAX_PARAMS for the loss, + 1 for the count).  Call after a block barrier that follows the last warp_partial.
+// Shared by every scaled driver of the fit, so they agree bit for bit.
+// tag != 0: every entry is written as two 8-byte words {low half, tag}, {high half, tag} (dst counts 16-byte
+// entries), so that a reader polling for `tag` needs no barrier and no fence (8-byte accesses are single-copy atomic).
 template <int NET>
-__device__ __forceinline__ void block_reduce_to(const Grads<NET>& g, float loss, uint32_t n, double* __restrict__ dst) {
-    __shared__ float s_red[kFitThreads / 32][Net<NET>::P + 2];
-    block_partial<NET>(g, loss, n, s_red, dst, 1);
+__device__ __forceinline__ void block_publish(const float (&s_red)[kMaxSeg][kFitThreads / 32][Net<NET>::P + 2], int n_seg,
+                                              double* __restrict__ dst, size_t seg_stride, size_t stride, unsigned int tag = 0u) {
+    constexpr int P = Net<NET>::P;
+    constexpr int N = P + 2;
+    for (int item = threadIdx.x; item < n_seg * N; item += kFitThreads) {
+        const int sv = item / N, q = item - sv * N;
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[sv][w][q];
+        const size_t at = (size_t)sv * seg_stride + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * stride;
+        if (tag) st_tagged(dst + 2 * at, t, tag); else dst[at] = t;
+    }
 }
 
 // Raw inputs of one sample, as loaded (conversion to the network's fp32 happens when the sample is used).
@@ -698,6 +707,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
 
     RawSample<NET, T> first[kFitUnroll<NET>];
     load_first_tile<NET, T>(seg_args<T>(a, 0), blockIdx.x, first);
+    __shared__ float s_red[kMaxSeg][kFitThreads / 32][N::P + 2];
     for (int v = 0; v < a.n_seg; ++v) {                   // one UNIT (fp32 accumulators of this block) per segment
         Grads<NET> g;
         g.zero();
@@ -705,9 +715,10 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
         uint32_t n = 0;
         accumulate_tiles<NET, LOSS, T, SKIP>(seg_args<T>(a, v), s_wa, blockIdx.x, gridDim.x, first, g, loss, n);
         if (v + 1 < a.n_seg) load_first_tile<NET, T>(seg_args<T>(a, v + 1), blockIdx.x, first);
-        if (v) __syncthreads();                            // the previous unit's shared-memory totals have been read
-        block_reduce_to<NET>(g, loss, n, partials + ((size_t)v * gridDim.x + blockIdx.x) * kGsum);
+        warp_partial<NET>(g, loss, n, s_red[v][threadIdx.x >> 5]);
     }
+    __syncthreads();
+    block_publish<NET>(s_red, a.n_seg, partials + (size_t)blockIdx.x * kGsum, (size_t)gridDim.x * kGsum, 1);
     if (STEP) {
         __shared__ bool s_last;
         __shared__ double s_g[kGsumLen];
@@ -853,7 +864,8 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     __shared__ float s_best[ORP_FIT_MAX_PARAMS];
     __shared__ double s_g[kGsumLen];
     __shared__ double s_c[16];                     // head of the control block (ST_LR .. ST_COUNT_ACC)
-    __shared__ float s_red[kFitThreads / 32][P + 2];
+    __shared__ double s_seg[kGsumLen][kMaxSeg];    // owner stage: segment totals of the columns this block owns
+    __shared__ float s_red[kMaxSeg][kFitThreads / 32][P + 2];
     __shared__ float s_lr_t;
     __shared__ int s_improved;
     __shared__ double s_num[kFitThreads], s_den[kFitThreads];      // Adam bias terms of the next 256 steps
@@ -915,10 +927,10 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                     const FitArgs a_next = part_args<T>(r, same_step ? sg + 1 : 0, same_step ? k : (k + 1 < r.n_parts ? k + 1 : 0), G, g_next);
                     load_first_tile<NET, T>(a_next, blockIdx.x, first);
                 }
-                if (sg) __syncthreads();                                        // s_red of the previous unit has been read
-                if (blockIdx.x < g_k)
-                    block_partial<NET>(g, loss, n, s_red, part + ((size_t)sg * kGsumLen * kLLBlocks + blockIdx.x) * 2, kLLBlocks, tag);
+                if (blockIdx.x < g_k) warp_partial<NET>(g, loss, n, s_red[sg][warp]);
             }
+            __syncthreads();
+            if (blockIdx.x < g_k) block_publish<NET>(s_red, n_seg, part + 2 * blockIdx.x, (size_t)kGsumLen * kLLBlocks, kLLBlocks, tag);
             ORP_TRACE(1);
             ORP_TRACE(2);
             // the step's learning rate: Adam bias terms from a table that all threads refill together every 256 steps
@@ -948,48 +960,57 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             const unsigned int fpar = step_id & 1u;
             // (owners are taken from the TOP of the grid: when the tiles do not divide evenly the low-numbered blocks carry
             //  the extra tile and finish last — they should not also have a column to add up)
-            for (int q = (int)(G - 1 - blockIdx.x) + warp * (int)G; q < P + 2; q += 8 * (int)G) {
+            // A block owns the columns q = G - 1 - b, + G, ...; its (column, segment) pairs are spread over its warps, so the
+            // eight segments of a column are polled side by side.
+            const int q_first = (int)(G - 1 - blockIdx.x);
+            const int n_own = q_first < P + 2 ? (P + 2 - q_first + (int)G - 1) / (int)G : 0;
+            for (int item = warp; item < n_own * n_seg; item += kFitThreads / 32) {
+                const int j = item / n_seg, sv = item - j * n_seg, q = q_first + j * (int)G;
                 const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
-                double seg[kMaxSeg];
-                bool ok = true;
+                const double* col = part + ((size_t)sv * kGsumLen + qq) * kLLBlocks * 2;
                 const unsigned long long t_start = globaltimer_ns();
+                double t = 0.0;
+                bool ok = true;
+                for (uint32_t b0 = 0; b0 < g_k && ok; b0 += 160) {
+                    // every retry re-reads ALL of this lane's entries at once (independent loads: one L2 round trip per
+                    // retry), so the total is ready at most two round trips after the last block has published
+                    uint4 v[5];
+                    unsigned int spins = 0;
+                    for (;;) {
+                        bool ready = true;
 #pragma unroll
-                for (int sv = 0; sv < kMaxSeg; ++sv) {                         // per segment: the blocks' entries in the fixed order
-                    double t = 0.0;
-                    if (sv < n_seg && ok) {
-                        const double* col = part + ((size_t)sv * kGsumLen + qq) * kLLBlocks * 2;
-                        for (uint32_t b0 = 0; b0 < g_k && ok; b0 += 160) {
-                            // every retry re-reads ALL of this lane's entries at once (independent loads: one L2 round trip
-                            // per retry), so the total is ready at most two round trips after the last block has published
-                            uint4 v[5];
-                            unsigned int spins = 0;
-                            for (;;) {
-                                bool ready = true;
+                        for (int jj = 0; jj < 5; ++jj) v[jj] = ld_tagged(col + 2 * (size_t)min(b0 + 32 * jj + lane, g_k - 1));
 #pragma unroll
-                                for (int j = 0; j < 5; ++j) v[j] = ld_tagged(col + 2 * (size_t)min(b0 + 32 * j + lane, g_k - 1));
-#pragma unroll
-                                for (int j = 0; j < 5; ++j) ready = ready && v[j].y == tag && v[j].w == tag;
-                                if (ready) break;
-                                if (((++spins & 255u) == 0u) && (poll_expired(t_start) || ld_acquire_u32(abort_flag) != 0u)) { ok = false; break; }
-                            }
-#pragma unroll
-                            for (int j = 0; j < 5; ++j) t += b0 + 32 * j + lane < g_k ? __hiloint2double((int)v[j].z, (int)v[j].x) : 0.0;
-                        }
-                        ok = __all_sync(0xffffffffu, ok);
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+                        for (int jj = 0; jj < 5; ++jj) ready = ready && v[jj].y == tag && v[jj].w == tag;
+                        if (ready) break;
+                        if (((++spins & 255u) == 0u) && (poll_expired(t_start) || ld_acquire_u32(abort_flag) != 0u)) { ok = false; break; }
                     }
-                    seg[sv] = t;
+#pragma unroll
+                    for (int jj = 0; jj < 5; ++jj) t += b0 + 32 * jj + lane < g_k ? __hiloint2double((int)v[jj].z, (int)v[jj].x) : 0.0;
                 }
-                if (!ok) { if (lane == 0) { atomicExch(abort_flag, 1u); s_peer_ok = 0; } continue; }
-                double t = tree_sum<kMaxSeg>(seg, n_seg);                      // the segments' totals, pairwise in segment order
-                t = __shfl_sync(0xffffffffu, t, 0);
-                if (lane < n_ranks) {
-                    double* dst = (r.world > 0 ? r.peers[lane] + kPeerSlots : ll_final)
-                                  + (((size_t)fpar * kPeerMaxWorld + my_rank) * kGsumLen + qq) * 2;
-                    st_tagged(dst, t, step_id);
+                ok = __all_sync(0xffffffffu, ok);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) t += __shfl_down_sync(0xffffffffu, t, o);
+                if (lane == 0) {
+                    s_seg[j][sv] = t;
+                    if (!ok) { atomicExch(abort_flag, 1u); s_peer_ok = 0; }
                 }
             }
+            __syncthreads();
+            if (s_peer_ok)
+                for (int j = warp; j < n_own; j += kFitThreads / 32) {
+                    const int q = q_first + j * (int)G;
+                    const int qq = q < P ? q : ORP_FIT_MAX_PARAMS + (q - P);
+                    double seg[kMaxSeg];
+#pragma unroll
+                    for (int sv = 0; sv < kMaxSeg; ++sv) seg[sv] = sv < n_seg ? s_seg[j][sv] : 0.0;
+                    const double t = tree_sum<kMaxSeg>(seg, n_seg);            // the segments' totals, pairwise in segment order
+                    if (lane < n_ranks) {
+                        double* dst = (r.world > 0 ? r.peers[lane] + kPeerSlots : ll_final)
+                                      + (((size_t)fpar * kPeerMaxWorld + my_rank) * kGsumLen + qq) * 2;
+                        st_tagged(dst, t, step_id);
+                    }
+                }
             ORP_TRACE(4);
             // ---- every block: wait for the ranks' totals in its OWN GPU's memory and add them in rank order (same bits
             //      everywhere).  ONE thread per block watches one entry (a different column per block, so the watchers
