@@ -113,17 +113,34 @@ class ReplicationNet:
     def _setup_peers(self):
         """Exchange buffers for the in-kernel all-gather of the [gradient, loss, count] vectors: every rank creates
         one (the library cudaMallocs it: CUDA IPC needs its own base allocation), the 64-byte IPC handles travel
-        through torch.distributed, and each rank maps the others' buffers.  Single process: a world of one."""
+        through torch.distributed, and each rank maps the others' buffers.  Single process: a world of one.
+
+        The exchange needs every rank on ONE host with peer access between all GPUs.  The ranks agree on that before
+        anything is mapped (host names and ``can_device_access_peer`` are gathered, the outcome of the mapping is
+        all-reduced); if any rank cannot take part, every rank undoes its mappings and the fit falls back to the
+        two-stage form (``orp_fit_grad`` -> collective -> ``orp_fit_update``), which needs nothing of the kind."""
         torch = _lib.require_cuda()
         L = _lib.lib()
         rank, world = rank_world(self.group)
         with torch.cuda.device(self.device):
+            if world > 1:
+                import socket
+                import torch.distributed as dist
+                dev_index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+                info = [None] * world
+                dist.all_gather_object(info, (socket.gethostname(), dev_index), group=self.group)
+                same_host = all(h == info[0][0] for h, _ in info)
+                reach = same_host and all(d == dev_index or torch.cuda.can_device_access_peer(dev_index, d) for _, d in info)
+                flag = torch.tensor([1.0 if reach else 0.0], device=self.device)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+                if float(flag) == 0.0:
+                    self.peers = None
+                    return
             own = C.c_void_p()
             handle = (C.c_ubyte * 64)()
             _lib.check(L.orp_peer_buffer_create(C.byref(own), handle))
-            ptrs, opened = [None] * world, []
+            ptrs, opened, ok = [None] * world, [], True
             if world > 1:
-                import torch.distributed as dist
                 handles = [None] * world
                 dist.all_gather_object(handles, bytes(handle), group=self.group)
                 for r, h in enumerate(handles):
@@ -131,14 +148,22 @@ class ReplicationNet:
                         continue
                     q = C.c_void_p()
                     buf = (C.c_ubyte * 64).from_buffer_copy(h)
-                    _lib.check(L.orp_peer_buffer_open(buf, C.byref(q)))
+                    if L.orp_peer_buffer_open(buf, C.byref(q)) != _lib.ORP_OK:
+                        ok = False
+                        break
                     ptrs[r] = q.value
                     opened.append(q.value)
+                flag = torch.tensor([1.0 if ok else 0.0], device=self.device)
+                dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)     # also: nobody starts before every mapping exists
+                if float(flag) == 0.0:
+                    for q in opened:
+                        L.orp_peer_buffer_close(q)
+                    dist.barrier(group=self.group)                                # every rank has unmapped before anyone frees
+                    L.orp_peer_buffer_destroy(own.value)
+                    self.peers = None
+                    return
             ptrs[rank] = own.value
             table = torch.tensor(ptrs, dtype=torch.int64, device=self.device)
-            if world > 1:
-                import torch.distributed as dist
-                dist.barrier(group=self.group)        # nobody starts exchanging before every mapping exists
         self.peers = dict(rank=rank, world=world, own=own.value, opened=opened, table=table)
 
     def close(self):
