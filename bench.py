@@ -34,10 +34,31 @@ import numpy as np  # noqa: E402
 
 METRIC = "path-steps/sec"
 CFG = dict(S0=100.0, K=100.0, T=1.0, r=0.05, sigma=0.2, D=252)
-FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12     # SIMT fp32 FMA peak at max clock (not in MEASURED_PEAKS.json)
+FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12     # SIMT fp32 FMA peak at max clock (MEASURED_PEAKS.json has no fp32 figure:
+                                                          # the run measures its own with orp_probe_throughput, see fp32_peak_measured)
 FIT_FLOP_PER_SAMPLE = 2 * 232 + 56                        # 232 multiply-adds + 56 elementwise ops per sample (EO net, fwd+bwd)
 FIT_FMA_PIPE_SLOTS = 144 * 2                              # FMA-pipe issue cycles per warp-sample: 144 packed FFMA2/FMUL2/FADD2-class ops, 2 cycles each
 FIT_PEAK_SAMPLES_PER_S = 148 * 4 * 32 * 1.965e9 / FIT_FMA_PIPE_SLOTS     # what the FMA pipe allows at max clock
+
+
+def fp32_peak_measured():
+    """Packed-FMA (fma.rn.f32x2) peak of THIS GPU in TFLOP/s, measured in this process with the library's probe kernel
+    (csrc/orp_probe.cu; best of 5 launches of ~10 ms, CUDA events): the denominator of the fit kernel's roofline."""
+    import ctypes as C
+    import torch
+    from orp_b200 import _lib
+    L = _lib.lib()
+    sink = torch.zeros(4, dtype=torch.float32, device="cuda")
+    n = C.c_double()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 0.0
+    for _ in range(6):
+        e0.record()
+        _lib.check(L.orp_probe_throughput(0, 2000, _lib.ptr(sink), C.byref(n), _lib.stream_ptr()))
+        e1.record()
+        torch.cuda.synchronize()
+        best = max(best, n.value / (e0.elapsed_time(e1) * 1e-3))
+    return best * 32 * 4 / 1e12                 # warp instructions/s x 32 lanes x 2 FMAs x 2 flop
 
 
 def measured_peaks():
@@ -49,15 +70,16 @@ def measured_peaks():
 
 
 def profiled_traffic(m, D):
-    """dram bytes (read + write) of one paths_kernel launch of THIS workload from the committed `ncu --set full`
-    summary (profiles/r01_paths_kernel_traffic.json), else None."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r01_paths_kernel_traffic.json")) as f:
-            t = json.load(f)
-        if t.get("paths_log2") == m and t.get("path_steps") == D:
-            return t["dram_bytes_read"] + t["dram_bytes_write"]
-    except (OSError, KeyError, ValueError):
-        pass
+    """dram bytes (read + write) of one paths_kernel launch of THIS workload from the newest committed `ncu --set full`
+    summary (profiles/r0N_paths_kernel_traffic.json), else None."""
+    for name in ("r02_paths_kernel_traffic.json", "r01_paths_kernel_traffic.json"):
+        try:
+            with open(os.path.join(ROOT, "profiles", name)) as f:
+                t = json.load(f)
+            if t.get("paths_log2") == m and t.get("path_steps") == D:
+                return t["dram_bytes_read"] + t["dram_bytes_write"]
+        except (OSError, KeyError, ValueError):
+            pass
     return None
 
 
@@ -117,18 +139,26 @@ class Pipeline:
         self.sweep_c = np.tile(np.minimum(np.arange(1, 9) * (D // 8) + D % 8, D), 8)
 
     def sweep(self, reps=5):
-        """Options priced per second (north_star's second throughput figure): 64 (strike, maturity) pairs sharing this
-        rank's stored paths; device time of the payoff-and-reduction kernels, all-reduce of the 128 sums included."""
+        """Options priced per second (north_star's second throughput figure): 64 (strike, maturity) pairs, (a) off this
+        rank's STORED paths (payoff_partial + payoff_final kernels) and (b) straight from the Sobol engine with the fused
+        generate + payoff kernel that never stores a path (C4 as BASELINE words it: generation included).  Device time,
+        one all-reduce of the packed sums per call included."""
         torch, orp = self.torch, self.orp
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        orp.price_european(self.paths, self.sweep_k, self.sweep_c, "call", r=CFG["r"], dt=CFG["T"] / self.D, total_paths=2 ** self.m)
-        e0.record()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        kw = dict(r=CFG["r"], total_paths=2 ** self.m)
+        orp.price_european(self.paths, self.sweep_k, self.sweep_c, "call", dt=CFG["T"] / self.D, **kw)
+        e[0].record()
         for _ in range(reps):
-            prices, _ = orp.price_european(self.paths, self.sweep_k, self.sweep_c, "call", r=CFG["r"], dt=CFG["T"] / self.D,
-                                           total_paths=2 ** self.m)
-        e1.record()
+            prices, _ = orp.price_european(self.paths, self.sweep_k, self.sweep_c, "call", dt=CFG["T"] / self.D, **kw)
+        e[1].record()
+        fkw = dict(steps=self.D, start=self.start, count=self.count, device=self.device, **kw)
+        orp.price_european_fused("gbm_log", self.sim, self.sweep_k, self.sweep_c, "call", **fkw)
+        e[2].record()
+        for _ in range(reps):
+            fused, _ = orp.price_european_fused("gbm_log", self.sim, self.sweep_k, self.sweep_c, "call", **fkw)
+        e[3].record()
         torch.cuda.synchronize()
-        return 64 * reps / (e0.elapsed_time(e1) * 1e-3), prices
+        return 64 * reps / (e[0].elapsed_time(e[1]) * 1e-3), prices, 64 * reps / (e[2].elapsed_time(e[3]) * 1e-3), fused
 
     def step(self, fresh_engine=False):
         torch, orp = self.torch, self.orp
@@ -175,7 +205,9 @@ def cpu_baseline(m_sample, D, threads=1, batch_size=512, start=0):
     bond = opaths.bond_curve(CFG["r"], CFG["T"], D + 1)
     res = ofit.backward_replication(S, bond, pay / CFG["S0"], net="eo", scale=CFG["S0"], batch_size=batch_size)
     t = time.perf_counter() - t0
-    return dict(value=n * D / t, seconds=t, seconds_paths=t_paths, V0=res["V0"] * CFG["S0"],
+    epochs = int(sum(h["epochs_run"] for h in res["history"]))
+    return dict(value=n * D / t, seconds=t, seconds_paths=t_paths, V0=res["V0"] * CFG["S0"], epochs=epochs,
+                adam_steps=epochs * -(-n // batch_size),
                 price_mc=float(np.exp(-CFG["r"] * CFG["T"]) * pay.mean()),
                 sample=f"2^{m_sample} of the 2^26 paths x {D} steps, same pipeline (paths + payoff + {D} fits, batch {batch_size})")
 
@@ -187,7 +219,7 @@ def _cpu_chunk(sim, D, start, count):
 
 def _cpu_replica(m_sample, D, k):
     r = cpu_baseline(m_sample, D, threads=1, start=k * 2 ** m_sample)
-    return r["seconds"], r["V0"], r["price_mc"]
+    return r["seconds"], r["V0"], r["price_mc"], r["epochs"], r["adam_steps"]
 
 
 def run_reference(args):
@@ -219,15 +251,19 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "path-steps/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args.m, D), "paths_log2": args.m, "path_steps": D,
-                       "note": "each step is a bounded sample of the workload"},
+            "config": config_dict(args.m, D, args.gpus),
             "cpu_baseline": {"value": value, "unit": "path-steps/s", "cores": cores, "kind": "port", "sample": sample,
                              "host_cores": os.cpu_count(), "per_core_path_steps_per_s": one_core,
                              "note": "the reference's fit is serial (512-sample Adam steps on 8-wide layers; intra-op threads slow "
                                      "it down), so all cores are used the only way it allows: independent processes, one window "
                                      "of paths each"},
             "e2e": {"value": value, "unit": "path-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "check": {"V0": float(np.mean([r[1] for r in last])), "price_mc": float(np.mean([r[2] for r in last]))}}
+            "check": {"V0": float(np.mean([r[1] for r in last])), "price_mc": float(np.mean([r[2] for r in last])),
+                      "epochs_per_window": float(np.mean([r[3] for r in last])), "adam_steps_per_window": float(np.mean([r[4] for r in last])),
+                      "samples_per_adam_step": 512, "windows": cores, "paths_per_window": n,
+                      "note": "work per path: the reference's Keras schedule (batch 512, shuffled) runs epochs_per_window epochs of "
+                              "paths_per_window / 512 Adam steps on each window; the GPU arm runs its epochs (fit_kernel.epochs_per_step) "
+                              "of 8 Adam steps over all 2^m paths"}}
     print(json.dumps(line))
     return 0
 
@@ -240,6 +276,13 @@ def sweep_err(prices, pipe):
         return CFG["S0"] * N(d1) - K * exp(-CFG["r"] * T) * N(d1 - CFG["sigma"] * sqrt(T))
     ref = np.array([bs(k, c * CFG["T"] / pipe.D) for k, c in zip(pipe.sweep_k, pipe.sweep_c)])
     return float(np.abs(np.asarray(prices) - ref).max())
+
+
+def config_dict(m, D, world):
+    """The `config` object of BOTH arms (the reference arm times a bounded sample of this workload, see its cpu_baseline)."""
+    return {"workload": workload_name(m, D), "paths_log2": m, "path_steps": D,
+            "parallelism": f"paths sharded x{world} by Sobol index range",
+            "l2": "inputs larger than L2 (the path array is read back by the fits; >= 16 GB per GPU)"}
 
 
 def workload_name(m, D):
@@ -287,18 +330,20 @@ def run_own(args):
     # end to end through the public API: host-side engine set-up (NumPy bit stream + integer scramble) + H2D of its
     # tables + pipeline + D2H of the results, every step
     barrier()
-    n_e2e = max(1, min(args.steps, 2))
+    n_e2e = args.steps
     ev[2].record()
     for _ in range(n_e2e):
         pipe.step(fresh_engine=True)
     ev[3].record()
     barrier()
     e2e_elapsed = ev[2].elapsed_time(ev[3]) * 1e-3 / n_e2e
-    opts_per_s, sweep_prices = pipe.sweep()
-    tt = torch.tensor([elapsed, e2e_elapsed, 1.0 / opts_per_s], dtype=torch.float64, device=device)
+    opts_per_s, sweep_prices, fused_per_s, fused_prices = pipe.sweep()
+    fp32_peak = fp32_peak_measured()
+    tt = torch.tensor([elapsed, e2e_elapsed, 1.0 / opts_per_s, 1.0 / fused_per_s, -fp32_peak], dtype=torch.float64, device=device)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    elapsed, e2e_elapsed, inv_opts = (float(x) for x in tt.cpu())
+    elapsed, e2e_elapsed, inv_opts, inv_fused, neg_peak = (float(x) for x in tt.cpu())
+    fp32_peak = -neg_peak                                      # the slowest GPU's packed-FMA peak
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -320,16 +365,19 @@ def run_own(args):
         "metric": METRIC, "value": total_steps / (ms / 1e3), "unit": "path-steps/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(m, D), "paths_log2": m, "path_steps": D, "parallelism": f"paths sharded x{world} by Sobol index range",
-                   "l2": "inputs larger than L2 (the path array is read back by the fits; >= 16 GB per GPU)"},
+        "config": config_dict(m, D, world),
         "roofline": {"kernel": "paths_kernel<GBM_LOG,double>", "bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"],
                      "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": profiled_traffic(m, D) if world == 1 else None,
                      "peak_kind": peak_kind + " (burst copy figure)",
                      "algorithmic_bytes_per_launch": path_bytes, "ms_per_launch": t_paths,
                      "note": "north_star's HBM-bound kernel; by TIME the step is dominated by the fit kernel, which is bound by the "
                              "fp32 FMA pipe (width-8 layers: SIMT by north_star's own rule), see fit_kernel"},
-        "fit_kernel": {"kernel": "fit_run_kernel<EO,MSE,double> (persistent, one launch per Model.fit)", "bound": "fp32 FMA pipe (packed FFMA2), not hbm/tensor: width-8 layers",
-                       "tflops": fit_flops / (t_fit * 1e-3) / 1e12, "peak_nominal_tflops": FP32_NOMINAL_TFLOPS,
+        "fit_kernel": {"kernel": "fit_run_kernel<EO,MSE,float> (persistent, one launch per Model.fit; fp32 price columns in network units)",
+                       "bound": "fp32 FMA pipe (packed FFMA2), not hbm/tensor: width-8 layers",
+                       "tflops": fit_flops / (t_fit * 1e-3) / 1e12, "peak_measured_tflops": fp32_peak,
+                       "frac_of_measured_fp32_peak": fit_flops / (t_fit * 1e-3) / 1e12 / fp32_peak,
+                       "peak_how": "fma.rn.f32x2 register loop on every SM, measured in this run (orp_probe_throughput)",
+                       "peak_nominal_tflops": FP32_NOMINAL_TFLOPS,
                        "epochs_per_step": epochs, "samples_per_s_per_gpu": 2 ** m / world * epochs / (t_fit * 1e-3),
                        "fma_pipe_peak_samples_per_s": FIT_PEAK_SAMPLES_PER_S,
                        "frac_of_fma_pipe": 2 ** m / world * epochs / (t_fit * 1e-3) / FIT_PEAK_SAMPLES_PER_S,
@@ -340,7 +388,13 @@ def run_own(args):
                 "d2h_bytes_per_step": int(16 + 16 * 8 * (D + 2) + 32 * D)},
         "options_priced_per_s": {"value": 1.0 / inv_opts, "what": "64 European calls (8 strikes x 8 maturities) off the stored path set of this "
                                  "workload, payoff_partial + payoff_final kernels + all-reduce (C4-shaped sweep)",
-                                 "max_abs_err_vs_black_scholes": sweep_err(sweep_prices, pipe)},
+                                 "max_abs_err_vs_black_scholes": sweep_err(sweep_prices, pipe),
+                                 "fused_generate_payoff": {"value": 1.0 / inv_fused, "what": "the same 64 calls straight from the Sobol engine: "
+                                                           "paths_payoff_kernel generates the 2^%d x %d path-steps, pays off and reduces without storing a path "
+                                                           "(0 B of path traffic)" % (m, D),
+                                                           "equivalent_path_steps_per_s": total_steps / (64 * inv_fused),
+                                                           "equivalent_GBps": 8 * total_steps / (64 * inv_fused) / 1e9,
+                                                           "max_rel_diff_vs_stored_sweep": float(np.abs(np.asarray(fused_prices) / np.asarray(sweep_prices) - 1).max())}},
         "gpu_launches": int(sum(s["launches"] for s in stages)),
         "clocks": clocks,
         "result": {"V0_nn": last["V0"], "phi0": last["phi0"], "psi0": last["psi0"], "price_mc": last["price_mc"], "p_otm": last["p_otm"]},

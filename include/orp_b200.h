@@ -126,6 +126,20 @@ int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, uint64_t coun
                       const double* strikes, const int32_t* cols, int32_t n_cols, double s0, double value_scale,
                       float* d_values_out, double* d_sums, double* d_otm, void* d_scratch, void* stream);
 
+/* Fused generate + payoff: the paths are NEVER stored (north_star: "keeps them in registers/shared memory when the
+ * payoff is fused").  Replaces, in one kernel, sobol_norm + the Euler loop (the model's lines as for orp_paths) AND the
+ * payoff block (European Options.ipynb cell 8 raw 328-329, 344, 347; Replicating_Portfolio.py:88-89) for up to
+ * ORP_MAX_OPTIONS (strike, maturity) pairs on ONE path set: option j pays off at time step steps[j] in [0, n_steps]
+ * (a fine-grid step, not a kept column: keep_every and out_dtype of `p` are ignored, ordering must be incremental).
+ * d_sums[j] = sum_i payoff(S_i(steps[j]), strikes[j]), d_otm[j] = out-of-the-money count (FLOOR: S < s0), as
+ * orp_payoff_reduce defines them; results agree with orp_paths + orp_payoff_reduce to summation order (1e-12).
+ * d_scratch: orp_paths_payoff_scratch_bytes(n_opt) bytes (per-block partial sums, fixed-order second pass). */
+uint64_t orp_paths_payoff_scratch_bytes(int n_opt);
+int orp_paths_payoff(const orp_path_params* p, const uint32_t* d_sv32, const uint32_t* d_tlane,
+                     const uint32_t* d_sv32_b, const uint32_t* d_tlane_b, uint64_t start, uint64_t count,
+                     int kind, int n_opt, const double* strikes, const int32_t* steps, double s0,
+                     double* d_sums, double* d_otm, void* d_scratch, void* stream);
+
 /* No counterpart in the reference.  Same computation and results as orp_payoff_reduce for callers that cannot
  * allocate device memory when they price — e.g. a service that gives all of the GPU to fixed arenas at start-up
  * and bans the runtime allocator afterwards, or a plug-in inside a framework whose allocator it may not use — and

@@ -7,6 +7,7 @@
 #include "orp_common.h"
 #include "orp_device.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <utility>
@@ -263,6 +264,202 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_kernel(const PathArgs a
 
 
 // ------------------------------------------------------------------------------------------------
+// Fused generate + payoff (north_star: "keeps them in registers/shared memory when the payoff is fused"; SURVEY 7.1
+// K3 "fused as K2's epilogue so paths are never written").  Same tile shape, skip-ahead and step arithmetic as
+// paths_kernel, but nothing is stored: at the time steps the options mature the two prices of a lane are paid off
+// against that step's strikes (groups of <= 8 options sharing a maturity), the group's sums are reduced over the warp
+// (reduce-scatter of the 8 doubles + two butterfly stages: 18 shuffles; the out-of-the-money tallies by integer warp
+// reduction) and added to the warp's own accumulators in shared memory — a fixed order, so every launch gives the
+// same bits.  Payoff formulas and NaN rules are those of payoff_partial_kernel (EO cell 8 raw 328-329, 344; RP.py:88-89).
+// Algorithmic HBM traffic: none (a few KB of tables); the kernel is bound by the fp64 / shared-memory work of the
+// path generation itself.
+constexpr int kFusedGroup = 8;
+
+struct FusedPayoff {
+    int n_opt, n_groups, kind;
+    double s0;                                   // FLOOR: out of the money means S < s0 (RP.py:89)
+    double* partials;                            // [gridDim.x][n_opt][2]
+    int32_t grp_step[ORP_MAX_OPTIONS];           // maturity (time step) of group g, ascending
+    int16_t grp_first[ORP_MAX_OPTIONS], grp_n[ORP_MAX_OPTIONS];
+    double strikes[ORP_MAX_OPTIONS];             // in group order
+};
+
+__device__ __forceinline__ void fused_group(const FusedPayoff& f, int g, double p0, double p1, bool ok0, bool ok1, int lane,
+                                            double* __restrict__ w_sum, unsigned* __restrict__ w_otm, unsigned long long* __restrict__ w_nan) {
+    const int first = f.grp_first[g], n = f.grp_n[g];
+    const int KIND = f.kind;                     // uniform over the launch
+    double a[kFusedGroup];
+    unsigned nan_bits = 0u;
+    const bool nan0 = ok0 && p0 != p0, nan1 = ok1 && p1 != p1;
+#pragma unroll
+    for (int k = 0; k < kFusedGroup; ++k) {
+        double pay0 = 0.0, pay1 = 0.0;
+        unsigned out = 0u;
+        if (k < n) {
+            const double K = f.strikes[first + k];
+            if (KIND == ORP_PAYOFF_FLOOR) {
+                pay0 = p0 > K ? p0 : K;                                            // RP.py:88 (np.where: NaN -> K)
+                pay1 = p1 > K ? p1 : K;
+                out = (ok0 && p0 < f.s0 ? 1u : 0u) + (ok1 && p1 < f.s0 ? 1u : 0u);  // RP.py:89
+            } else {
+                const double d0 = KIND == ORP_PAYOFF_CALL ? p0 - K : K - p0, d1 = KIND == ORP_PAYOFF_CALL ? p1 - K : K - p1;
+                const bool in0 = d0 > 0.0, in1 = d1 > 0.0;                         // false for NaN
+                pay0 = in0 ? d0 : 0.0;
+                pay1 = in1 ? d1 : 0.0;
+                out = (ok0 && !in0 ? 1u : 0u) + (ok1 && !in1 ? 1u : 0u);
+                if (nan0 || nan1) nan_bits |= 1u << k;                             // np.maximum propagates NaN into the mean
+            }
+        }
+        a[k] = (ok0 ? pay0 : 0.0) + (ok1 ? pay1 : 0.0);
+        const unsigned tot = __reduce_add_sync(kFull, out);
+        if (lane == k && k < n) w_otm[first + k] += tot;
+    }
+    nan_bits = __reduce_or_sync(kFull, nan_bits);
+    if (lane == 0 && nan_bits) *w_nan |= (unsigned long long)nan_bits << first;
+    // reduce-scatter of the eight sums: after the stages with offsets 16, 8, 4 a lane holds the 8-lane partial of sum
+    // idx = 4 b4 + 2 b3 + b2 (bN: bit N of the lane index); two butterfly stages finish it
+    int len = kFusedGroup;
+#pragma unroll
+    for (int off = 16; off >= 4; off >>= 1) {
+        const int half = len / 2;
+        const bool up = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < kFusedGroup / 2; ++i)
+            if (i < half) {
+                const double lo = a[i], hi = a[i + half];
+                a[i] = (up ? hi : lo) + __shfl_xor_sync(kFull, up ? lo : hi, off);
+            }
+        len = half;
+    }
+    a[0] += __shfl_xor_sync(kFull, a[0], 2);
+    a[0] += __shfl_xor_sync(kFull, a[0], 1);
+    const int idx = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+    if ((lane & 3) == 0 && idx < n) w_sum[first + idx] += a[0];
+}
+
+template <int MODEL, bool FUSED, bool TLS>
+__global__ void __launch_bounds__(kPathThreads, 1) paths_payoff_kernel(const PathArgs a, const FusedPayoff f) {
+    static_assert(!FUSED || MODEL == ORP_MODEL_GBM_LOG, "only the log-Euler GBM step fuses into the table");
+    extern __shared__ __align__(128) char s_tab[];
+    constexpr int kWarps = kPathThreads / 32;
+    __shared__ double s_sum[kWarps][ORP_MAX_OPTIONS];
+    __shared__ unsigned s_otm[kWarps][ORP_MAX_OPTIONS];
+    __shared__ unsigned long long s_nan[kWarps];
+    load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
+    const int D = a.n_steps;
+    if (TLS) {
+        uint2* dst_a = reinterpret_cast<uint2*>(s_tab + kNdtriTableBytes);
+        const int n = (D + 1) * 32;
+        for (int i = threadIdx.x; i < n + 32; i += blockDim.x) dst_a[i] = i < n ? __ldg(a.tlane_a + i) : make_uint2(0u, 0u);
+        if (MODEL == ORP_MODEL_SV) {
+            uint2* dst_b = reinterpret_cast<uint2*>(s_tab + kNdtriTableBytes + tlane_smem_bytes(D));
+            for (int i = threadIdx.x; i < n + 32; i += blockDim.x) dst_b[i] = i < n ? __ldg(a.tlane_b + i) : make_uint2(0u, 0u);
+        }
+    }
+    for (int i = threadIdx.x; i < kWarps * ORP_MAX_OPTIONS; i += blockDim.x) { (&s_sum[0][0])[i] = 0.0; (&s_otm[0][0])[i] = 0u; }
+    if (threadIdx.x < kWarps) s_nan[threadIdx.x] = 0ull;
+    __syncthreads();
+    if (FUSED) {
+        fuse_gbm_table(s_tab, a.c_drift, a.c_vol, threadIdx.x, blockDim.x);
+        __syncthreads();
+    }
+
+    const uint32_t tab = (uint32_t)__cvta_generic_to_shared(s_tab);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t tls_a = tab + kNdtriTableBytes + lane * 8u;
+    const uint32_t tls_b = tls_a + (uint32_t)tlane_smem_bytes(D);
+    const uint64_t end = a.start + a.count;
+    const uint64_t w_first = a.start / kWarpPaths, w_last = (end - 1) / kWarpPaths;
+    const uint64_t n_tiles = w_last - w_first + 1;
+    double* const w_sum = s_sum[warp];
+    unsigned* const w_otm = s_otm[warp];
+
+    for (uint64_t tile = (uint64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (uint64_t)gridDim.x * kWarps) {
+        const uint64_t w = w_first + tile;
+        const uint64_t i0 = w * kWarpPaths + lane, i1 = i0 + 32;
+        const bool ok0 = i0 >= a.start && i0 < end, ok1 = i1 >= a.start && i1 < end;
+        double s_0, s_1, v_0 = a.v0, v_1 = a.v0;
+        if (kLevel<MODEL> || FUSED) s_0 = s_1 = a.s0; else s_0 = s_1 = log(a.s0);
+        int g = 0;
+        while (g < f.n_groups && f.grp_step[g] == 0) { fused_group(f, g, a.s0, a.s0, ok0, ok1, lane, w_sum, w_otm, &s_nan[warp]); ++g; }
+        int next_step = g < f.n_groups ? f.grp_step[g] : -1;
+
+        for (int t0 = 1; t0 <= D && g < f.n_groups; t0 += 32) {          // nothing matures later: stop walking
+            const int my_dim = t0 + lane;
+            uint32_t bl_a = 0u, bl_b = 0u;
+            if (my_dim <= D) {
+                bl_a = warp_base(a.sv32_a, a.dpad, my_dim, w);
+                if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, a.dpad, my_dim, w);
+            }
+            const int nc = min(32, D - t0 + 1);
+            uint32_t tp_a = tls_a + (uint32_t)t0 * 256u, tp_b = tls_b + (uint32_t)t0 * 256u;
+            uint2 tl_next = TLS ? lds_u32x2(tp_a) : __ldg(a.tlane_a + (size_t)t0 * 32 + lane);
+            uint2 tb_next = make_uint2(0u, 0u);
+            if (MODEL == ORP_MODEL_SV) tb_next = TLS ? lds_u32x2(tp_b) : __ldg(a.tlane_b + (size_t)t0 * 32 + lane);
+            for (int s = 0; s < nc; ++s) {
+                const int t = t0 + s;
+                const uint32_t base = __shfl_sync(kFull, bl_a, s);
+                const uint2 tl = tl_next;
+                if (TLS) { tp_a += 256u; tl_next = lds_u32x2(tp_a); }
+                else tl_next = __ldg(a.tlane_a + (size_t)min(t + 1, D) * 32 + lane);
+                if (FUSED) {
+                    s_0 *= table_eval(base ^ tl.x, tab);
+                    s_1 *= table_eval(base ^ tl.y, tab);
+                } else {
+                    const double z0 = ndtri_bits(base ^ tl.x, tab);
+                    const double z1 = ndtri_bits(base ^ tl.y, tab);
+                    double y0 = 0.0, y1 = 0.0;
+                    if (MODEL == ORP_MODEL_SV) {
+                        const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
+                        const uint2 tb = tb_next;
+                        if (TLS) { tp_b += 256u; tb_next = lds_u32x2(tp_b); }
+                        else tb_next = __ldg(a.tlane_b + (size_t)min(t + 1, D) * 32 + lane);
+                        y0 = ndtri_bits(base_b ^ tb.x, tab);
+                        y1 = ndtri_bits(base_b ^ tb.y, tab);
+                    }
+                    advance<MODEL, false>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
+                }
+                if (t == next_step) {                                       // warp-uniform
+                    double p0 = s_0, p1 = s_1;
+                    if (!kLevel<MODEL> && !FUSED) { p0 = exp(s_0); p1 = exp(s_1); }
+                    do {
+                        fused_group(f, g, p0, p1, ok0, ok1, lane, w_sum, w_otm, &s_nan[warp]);
+                        ++g;
+                    } while (g < f.n_groups && f.grp_step[g] == t);
+                    next_step = g < f.n_groups ? f.grp_step[g] : -1;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    // block totals: the warps' accumulators in warp order
+    for (int o = threadIdx.x; o < f.n_opt; o += blockDim.x) {
+        double t = 0.0;
+        unsigned c = 0u;
+        bool bad = false;
+        for (int wq = 0; wq < kWarps; ++wq) { t += s_sum[wq][o]; c += s_otm[wq][o]; bad = bad || ((s_nan[wq] >> o) & 1ull); }
+        f.partials[((size_t)blockIdx.x * f.n_opt + o) * 2] = bad ? __longlong_as_double(0x7ff8000000000000ll) : t;
+        f.partials[((size_t)blockIdx.x * f.n_opt + o) * 2 + 1] = (double)c;
+    }
+}
+
+struct FusedPerm { int16_t to_caller[ORP_MAX_OPTIONS]; };          // group-order index -> the caller's option index
+
+// second pass: one warp per (option, quantity); lane l adds blocks l, l + 32, ... in increasing order, then a shuffle tree
+__global__ void __launch_bounds__(128) paths_payoff_final_kernel(const double* __restrict__ partials, int n_blocks, int n_opt,
+                                                                 const FusedPerm perm, double* __restrict__ sums, double* __restrict__ otm) {
+    const int o = (blockIdx.x * 128 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (o >= 2 * n_opt) return;
+    const int opt = o >> 1, which = o & 1;
+    double t = 0.0;
+    for (int b = lane; b < n_blocks; b += 32) t += partials[((size_t)b * n_opt + opt) * 2 + which];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) t += __shfl_down_sync(kFull, t, off);
+    if (lane == 0) (which ? otm : sums)[perm.to_caller[opt]] = t;
+}
+
+
+// ------------------------------------------------------------------------------------------------
 // Brownian-bridge ordering (NEW feature; specification in oracle/bridge.py, no reference counterpart).
 // Sobol coordinates are random-access in the DIMENSION as well as in the index, so the bridge needs no
 // buffering of a path's D normals: the bisection tree is walked depth-first in time order with a stack
@@ -420,6 +617,47 @@ static int launch_paths_bridge(const PathArgs& a, const void* d_bridge, cudaStre
     return launch_paths_bridge_v<MODEL, OutT, false>(a, d_bridge, st);
 }
 
+// PathArgs of a launch from the caller's parameter block (shared by orp_paths and orp_paths_payoff)
+static int build_path_args(const orp_path_params* p, const uint32_t* d_sv32, const uint32_t* d_tlane, const uint32_t* d_sv32_b,
+                           const uint32_t* d_tlane_b, uint64_t start, uint64_t count, PathArgs& a) {
+    a.sv32_a = d_sv32;  a.tlane_a = reinterpret_cast<const uint2*>(d_tlane);
+    a.sv32_b = d_sv32_b; a.tlane_b = reinterpret_cast<const uint2*>(d_tlane_b);
+    a.out = nullptr; a.ld = 0; a.start = start; a.count = count;
+    a.n_steps = p->n_steps; a.keep_every = p->keep_every;
+    const int sobol_dim = p->sobol_dim > 0 ? p->sobol_dim : p->n_steps + 1;
+    ORP_REQUIRE(sobol_dim >= p->n_steps + 1 && sobol_dim <= ORP_SOBOL_MAXDIM, "sobol_dim must be in [n_steps + 1, %d]", ORP_SOBOL_MAXDIM);
+    a.dpad = ORP_SV_DPAD(sobol_dim);
+    a.s0 = p->s0; a.dt = p->dt; a.v0 = p->v0; a.a = p->a; a.b = p->b; a.c = p->c;
+    const double sqdt = sqrt(p->dt);
+    switch (p->model) {
+        case ORP_MODEL_GBM_LOG:   a.c_drift = (p->mu - 0.5 * p->sigma * p->sigma) * p->dt; a.c_vol = p->sigma * sqdt; break;
+        case ORP_MODEL_GBM_ARITH: a.c_drift = p->mu * p->dt;                              a.c_vol = p->sigma * sqdt; break;
+        case ORP_MODEL_SV:        a.c_drift = p->mu;                                      a.c_vol = sqdt;            break;
+        case ORP_MODEL_LINEAR:    a.c_drift = p->mu * p->dt;                              a.c_vol = p->sigma * sqdt; break;
+        default: return fail(ORP_E_VALUE, "unknown model %d", p->model);
+    }
+    return ORP_OK;
+}
+
+template <int MODEL, bool FUSED>
+static int launch_paths_payoff(const PathArgs& a, const FusedPayoff& f, int grid, cudaStream_t st) {
+    const size_t engines = MODEL == ORP_MODEL_SV ? 2 : 1;
+    const size_t with_tl = kNdtriTableBytes + engines * tlane_smem_bytes(a.n_steps);
+    // static shared memory of the kernel (the warps' accumulators) counts against the same 227 KB
+    const bool tls = with_tl + 26 * 1024 <= kMaxDynSmem && !getenv("ORP_B200_NO_TLS");
+    if (tls) {
+        int rc = set_table_smem(paths_payoff_kernel<MODEL, FUSED, true>, with_tl);
+        if (rc) return rc;
+        paths_payoff_kernel<MODEL, FUSED, true><<<grid, kPathThreads, with_tl, st>>>(a, f);
+    } else {
+        int rc = set_table_smem(paths_payoff_kernel<MODEL, FUSED, false>, kNdtriTableBytes);
+        if (rc) return rc;
+        paths_payoff_kernel<MODEL, FUSED, false><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a, f);
+    }
+    ORP_LAUNCH_CHECK("paths_payoff_kernel");
+    return ORP_OK;
+}
+
 }  // namespace orp
 
 using namespace orp;
@@ -520,22 +758,9 @@ extern "C" int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const
     if (count == 0) return ORP_OK;
 
     PathArgs a;
-    a.sv32_a = d_sv32;  a.tlane_a = reinterpret_cast<const uint2*>(d_tlane);
-    a.sv32_b = d_sv32_b; a.tlane_b = reinterpret_cast<const uint2*>(d_tlane_b);
-    a.out = d_out; a.ld = ld; a.start = start; a.count = count;
-    a.n_steps = p->n_steps; a.keep_every = p->keep_every;
-    const int sobol_dim = p->sobol_dim > 0 ? p->sobol_dim : p->n_steps + 1;
-    ORP_REQUIRE(sobol_dim >= p->n_steps + 1 && sobol_dim <= ORP_SOBOL_MAXDIM, "sobol_dim must be in [n_steps + 1, %d]", ORP_SOBOL_MAXDIM);
-    a.dpad = ORP_SV_DPAD(sobol_dim);
-    a.s0 = p->s0; a.dt = p->dt; a.v0 = p->v0; a.a = p->a; a.b = p->b; a.c = p->c;
-    const double sqdt = sqrt(p->dt);
-    switch (p->model) {
-        case ORP_MODEL_GBM_LOG:   a.c_drift = (p->mu - 0.5 * p->sigma * p->sigma) * p->dt; a.c_vol = p->sigma * sqdt; break;
-        case ORP_MODEL_GBM_ARITH: a.c_drift = p->mu * p->dt;                              a.c_vol = p->sigma * sqdt; break;
-        case ORP_MODEL_SV:        a.c_drift = p->mu;                                      a.c_vol = sqdt;            break;
-        case ORP_MODEL_LINEAR:    a.c_drift = p->mu * p->dt;                              a.c_vol = p->sigma * sqdt; break;
-        default: return fail(ORP_E_VALUE, "unknown model %d", p->model);
-    }
+    int rc = build_path_args(p, d_sv32, d_tlane, d_sv32_b, d_tlane_b, start, count, a);
+    if (rc) return rc;
+    a.out = d_out; a.ld = ld;
     if (p->ordering == ORP_ORDER_BRIDGE) {
         switch (p->model) {
             case ORP_MODEL_GBM_LOG:   return p->out_dtype == ORP_F32 ? launch_paths_bridge<ORP_MODEL_GBM_LOG, float>(a, d_bridge, (cudaStream_t)stream)   : launch_paths_bridge<ORP_MODEL_GBM_LOG, double>(a, d_bridge, (cudaStream_t)stream);
@@ -556,4 +781,72 @@ extern "C" int orp_paths(const orp_path_params* p, const uint32_t* d_sv32, const
         case ORP_MODEL_LINEAR:    return f32 ? launch_paths<ORP_MODEL_LINEAR, float>(a, st)    : launch_paths<ORP_MODEL_LINEAR, double>(a, st);
         default:                  return f32 ? launch_paths<ORP_MODEL_SV, float>(a, st)        : launch_paths<ORP_MODEL_SV, double>(a, st);
     }
+}
+
+static int fused_grid(uint64_t start, uint64_t count) {
+    const uint64_t n_tiles = (start + count - 1) / kWarpPaths - start / kWarpPaths + 1;
+    const uint64_t want = (n_tiles + 31) / 32;
+    return (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
+}
+
+extern "C" uint64_t orp_paths_payoff_scratch_bytes(int n_opt) {
+    if (n_opt < 1) n_opt = 1;
+    if (n_opt > ORP_MAX_OPTIONS) n_opt = ORP_MAX_OPTIONS;
+    return 1024ull * (uint64_t)n_opt * 2 * sizeof(double);       // one partial pair per option and block; <= 1024 blocks
+}
+
+extern "C" int orp_paths_payoff(const orp_path_params* p, const uint32_t* d_sv32, const uint32_t* d_tlane,
+                                const uint32_t* d_sv32_b, const uint32_t* d_tlane_b, uint64_t start, uint64_t count,
+                                int kind, int n_opt, const double* strikes, const int32_t* steps, double s0,
+                                double* d_sums, double* d_otm, void* d_scratch, void* stream) {
+    ORP_REQUIRE(p && d_sv32 && d_tlane && strikes && steps && d_sums && d_otm && d_scratch, "null pointer");
+    ORP_REQUIRE(p->n_steps >= 1 && p->n_steps + 1 <= ORP_SOBOL_MAXDIM, "n_steps must be in [1, %d]", ORP_SOBOL_MAXDIM - 1);
+    ORP_REQUIRE(count >= 1 && start + count <= (1ull << ORP_SOBOL_BITS), "At most 2**%d=%llu distinct points can be generated.",
+                ORP_SOBOL_BITS, 1ull << ORP_SOBOL_BITS);
+    ORP_REQUIRE(p->ordering == ORP_ORDER_INCREMENTAL, "the fused kernel walks the time axis in incremental order only");
+    ORP_REQUIRE(p->model != ORP_MODEL_SV || (d_sv32_b && d_tlane_b), "the SV model needs a second Sobol engine");
+    ORP_REQUIRE(n_opt >= 1 && n_opt <= ORP_MAX_OPTIONS, "n_opt must be in [1, %d]", ORP_MAX_OPTIONS);
+    ORP_REQUIRE(kind >= ORP_PAYOFF_CALL && kind <= ORP_PAYOFF_FLOOR, "unknown payoff kind %d", kind);
+    PathArgs a;
+    int rc = build_path_args(p, d_sv32, d_tlane, d_sv32_b, d_tlane_b, start, count, a);
+    if (rc) return rc;
+    // options grouped by maturity step (ascending, stable), at most kFusedGroup per group
+    FusedPayoff f;
+    FusedPerm perm;
+    int order[ORP_MAX_OPTIONS];
+    for (int k = 0; k < n_opt; ++k) {
+        ORP_REQUIRE(steps[k] >= 0 && steps[k] <= p->n_steps, "maturity step %d of option %d is outside [0, %d]", steps[k], k, p->n_steps);
+        order[k] = k;
+    }
+    std::stable_sort(order, order + n_opt, [&](int x, int y) { return steps[x] < steps[y]; });
+    f.n_opt = n_opt; f.kind = kind; f.s0 = s0; f.n_groups = 0;
+    f.partials = reinterpret_cast<double*>(d_scratch);
+    for (int k = 0; k < n_opt; ++k) {
+        const int o = order[k];
+        f.strikes[k] = strikes[o];
+        perm.to_caller[k] = (int16_t)o;
+        if (f.n_groups == 0 || f.grp_step[f.n_groups - 1] != steps[o] || f.grp_n[f.n_groups - 1] == kFusedGroup) {
+            f.grp_step[f.n_groups] = steps[o];
+            f.grp_first[f.n_groups] = (int16_t)k;
+            f.grp_n[f.n_groups] = 0;
+            ++f.n_groups;
+        }
+        f.grp_n[f.n_groups - 1] += 1;
+    }
+    int grid = fused_grid(start, count);
+    if (grid > 1024) grid = 1024;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (p->model) {
+        case ORP_MODEL_GBM_LOG:
+            if (fabs(a.c_vol) < 0.25 && fabs(a.c_drift) < 1.0 && !getenv("ORP_B200_NO_FUSE")) rc = launch_paths_payoff<ORP_MODEL_GBM_LOG, true>(a, f, grid, st);
+            else rc = launch_paths_payoff<ORP_MODEL_GBM_LOG, false>(a, f, grid, st);
+            break;
+        case ORP_MODEL_GBM_ARITH: rc = launch_paths_payoff<ORP_MODEL_GBM_ARITH, false>(a, f, grid, st); break;
+        case ORP_MODEL_LINEAR:    rc = launch_paths_payoff<ORP_MODEL_LINEAR, false>(a, f, grid, st); break;
+        default:                  rc = launch_paths_payoff<ORP_MODEL_SV, false>(a, f, grid, st); break;
+    }
+    if (rc) return rc;
+    paths_payoff_final_kernel<<<(2 * n_opt * 32 + 127) / 128, 128, 0, st>>>(f.partials, grid, n_opt, perm, d_sums, d_otm);
+    ORP_LAUNCH_CHECK("paths_payoff_final_kernel");
+    return ORP_OK;
 }

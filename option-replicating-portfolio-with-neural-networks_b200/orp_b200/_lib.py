@@ -68,6 +68,8 @@ PROTOTYPES = {
     "orp_payoff_scratch_bytes": (C.c_uint64, [_i32]),
     "orp_payoff_reduce": (C.c_int, [_vp, _i32, _u64, _u64, _i32, _i32, _vp, _vp, _i32, _f64, _f64, _vp, _vp, _vp, _vp, _vp]),
     "orp_payoff_reduce_noalloc": (C.c_int, [_vp, _i32, _u64, _u64, _i32, _i32, _vp, _vp, _i32, _f64, _f64, _vp, _vp, _vp, _vp]),
+    "orp_paths_payoff_scratch_bytes": (C.c_uint64, [_i32]),
+    "orp_paths_payoff": (C.c_int, [C.POINTER(PathParams), _vp, _vp, _vp, _vp, _u64, _u64, _i32, _i32, _vp, _vp, _f64, _vp, _vp, _vp, _vp]),
     "orp_fit_n_params": (C.c_int, [_i32]),
     "orp_fit_scratch_bytes": (C.c_uint64, []),
     "orp_fit_grad": (C.c_int, [C.POINTER(FitBatch), _vp, _vp, _vp, _vp, _vp]),

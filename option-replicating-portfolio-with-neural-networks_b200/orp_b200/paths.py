@@ -98,15 +98,7 @@ def simulate_paths(model: str, params: dict, m: int | None = None, steps: int | 
         raise ValueError("steps must be <= engine_dim - 1")
     n_cols = steps // keep_every + 1
     device = torch.device(device)
-    p = _lib.PathParams()
-    p.model, p.ordering, p.n_steps, p.keep_every = _lib.MODEL[model], _lib.ORDER[ordering], steps, keep_every
-    p.out_dtype = _DTYPES[dtype]
-    p.sobol_dim = d
-    p.s0 = float(params.get("S0", params.get("Y", 1.0)))
-    p.mu = float(params.get("mu", params.get("r", 0.0)))
-    p.sigma = float(params.get("sigma", 0.0))
-    p.dt = float(params["dt"])
-    p.v0, p.a, p.b, p.c = (float(params.get(k, 0.0)) for k in ("s0", "a", "b", "c"))
+    p = _path_params(model, params, steps, ordering, dtype, keep_every, d)
     tdt = torch.float64 if p.out_dtype == _lib.F64 else torch.float32
     with torch.cuda.device(device):
         sv_a, tl_a = engine(d, seed).device_tables(device)
@@ -174,6 +166,102 @@ def payoff_sums(paths_tm, strikes, columns, kind: str = "call", s0: float = 0.0,
             inv = torch.from_numpy(np.argsort(order)).to(paths_tm.device)
             sums, otm = sums[inv], otm[inv]
     return sums, otm
+
+
+def _path_params(model, params, steps, ordering, dtype, keep_every, engine_dim):
+    p = _lib.PathParams()
+    p.model, p.ordering, p.n_steps, p.keep_every = _lib.MODEL[model], _lib.ORDER[ordering], steps, keep_every
+    p.out_dtype = _DTYPES[dtype]
+    p.sobol_dim = steps + 1 if engine_dim is None else int(engine_dim)
+    p.s0 = float(params.get("S0", params.get("Y", 1.0)))
+    p.mu = float(params.get("mu", params.get("r", 0.0)))
+    p.sigma = float(params.get("sigma", 0.0))
+    p.dt = float(params["dt"])
+    p.v0, p.a, p.b, p.c = (float(params.get(k, 0.0)) for k in ("s0", "a", "b", "c"))
+    return p
+
+
+_fused_buffers = {}
+
+
+def payoff_sums_fused(model: str, params: dict, strikes, maturity_steps, kind: str = "call", m: int | None = None,
+                      steps: int | None = None, seed: int = 1235, shard=(0, 1), start: int | None = None,
+                      count: int | None = None, seed_sv: int = 1234, device="cuda", s0: float = 0.0,
+                      engine_dim: int | None = None):
+    """Generate the paths and pay the options off in ONE kernel, without storing a single path
+    (``orp_paths_payoff``): per option ``j`` the sum of ``payoff(S(maturity_steps[j]), strikes[j])`` over the index
+    range and the out-of-the-money count, as two fp64 CUDA tensors (views of per-device buffers that the next call
+    overwrites; no host sync).  Same models, engines and index-range arguments as :func:`simulate_paths`;
+    ``maturity_steps`` are fine-grid time steps in ``[0, steps]``.  Up to 64 options per call."""
+    torch = _lib.require_cuda()
+    if steps is None:
+        raise ValueError("steps is required")
+    steps = int(steps)
+    if start is None:
+        if m is None:
+            raise ValueError("give m or start/count")
+        start, count = shard_range(2 ** int(m), int(shard[0]), int(shard[1]))
+    _check_range(start, count)
+    if model not in _lib.MODEL:
+        raise ValueError(f"model must be one of {sorted(_lib.MODEL)}")
+    if kind not in _lib.PAYOFF:
+        raise ValueError(f"kind must be one of {sorted(_lib.PAYOFF)}")
+    strikes = np.ascontiguousarray(np.atleast_1d(strikes), dtype=np.float64)
+    mats = np.ascontiguousarray(np.atleast_1d(maturity_steps), dtype=np.int64)
+    if strikes.shape != mats.shape:
+        raise ValueError("strikes and maturity_steps must have the same length")
+    n_opt = strikes.size
+    if not 1 <= n_opt <= _lib.MAX_OPTIONS:
+        raise ValueError(f"between 1 and {_lib.MAX_OPTIONS} options per call")
+    mats = np.where(mats < 0, mats + steps + 1, mats)
+    if (mats < 0).any() or (mats > steps).any():
+        raise ValueError("maturity step out of range")
+    mats = np.ascontiguousarray(mats, dtype=np.int32)
+    d = steps + 1 if engine_dim is None else int(engine_dim)
+    if steps > d - 1:
+        raise ValueError("steps must be <= engine_dim - 1")
+    device = torch.device(device)
+    p = _path_params(model, params, steps, "incremental", "float64", 1, d)
+    with torch.cuda.device(device):
+        sv_a, tl_a = engine(d, seed).device_tables(device)
+        sv_b = tl_b = None
+        if model == "sv":
+            sv_b, tl_b = engine(d, seed_sv).device_tables(device)
+        key = str(device)
+        if key not in _fused_buffers:          # scratch and outputs live as long as the process: no allocation per call
+            _fused_buffers[key] = (torch.empty(_lib.lib().orp_paths_payoff_scratch_bytes(_lib.MAX_OPTIONS), dtype=torch.uint8, device=device),
+                                   torch.empty(2 * _lib.MAX_OPTIONS + 1, dtype=torch.float64, device=device))
+        scratch, out = _fused_buffers[key]
+        _lib.check(_lib.lib().orp_paths_payoff(C.byref(p), _lib.ptr(sv_a), _lib.ptr(tl_a), _lib.ptr(sv_b), _lib.ptr(tl_b),
+                                               start, count, _lib.PAYOFF[kind], n_opt, _lib.ptr(strikes), _lib.ptr(mats), float(s0),
+                                               _lib.ptr(out), _lib.ptr(out) + 8 * _lib.MAX_OPTIONS, _lib.ptr(scratch), _lib.stream_ptr()))
+    return out[:n_opt], out[_lib.MAX_OPTIONS:_lib.MAX_OPTIONS + n_opt]
+
+
+def price_european_fused(model: str, params: dict, strikes, maturity_steps, kind: str = "call", r: float = 0.0,
+                         m: int | None = None, steps: int | None = None, total_paths: int | None = None, group=None, **kw):
+    """Discounted Monte-Carlo prices ``exp(-r * dt * step) * mean(payoff)`` of up to 64 (strike, maturity step) pairs
+    straight from the Sobol engine: paths generated, paid off and reduced in one kernel, never stored
+    (:func:`payoff_sums_fused`); ONE all-reduce of the packed sums when ``torch.distributed`` is initialised.  Pass
+    ``shard=(rank, world)`` (or ``start``/``count``) as for :func:`simulate_paths`.  Returns ``(prices, prob_otm)``."""
+    torch = _lib.require_cuda()
+    sums, otm = payoff_sums_fused(model, params, strikes, maturity_steps, kind, m=m, steps=steps, **kw)
+    k = sums.numel()
+    packed = sums.new_empty(2 * k + 1)
+    packed[:k], packed[k:2 * k] = sums, otm
+    if kw.get("start") is not None:
+        n_local = kw["count"]
+    else:
+        n_local = shard_range(2 ** int(m), *(int(x) for x in kw.get("shard", (0, 1))))[1]
+    packed[2 * k] = float(n_local)
+    from .dist import allreduce_sum_
+    allreduce_sum_(packed, group)
+    packed = packed.cpu().numpy()
+    total = packed[-1] if total_paths is None else float(total_paths)
+    mats = np.atleast_1d(np.asarray(maturity_steps))
+    mats = np.where(mats < 0, mats + int(steps) + 1, mats)
+    disc = np.exp(-r * float(params["dt"]) * mats)
+    return disc * packed[:k] / total, packed[k:2 * k] / total
 
 
 def price_european(paths, strikes, maturities_idx, kind: str = "call", r: float = 0.0, dt: float = 1.0,

@@ -247,3 +247,59 @@ def test_c4_strike_maturity_sweep_64_options(cuda):
     bs = np.array([opaths.black_scholes_call(100.0, k, c / 252, 0.05, 0.2) for k, c in zip(strikes, cols)])
     assert np.abs(prices - bs).max() < 0.1              # QMC error of 2^14 paths in the far out-of-the-money corner
     assert ((p_otm >= 0) & (p_otm <= 1)).all()
+
+
+# ---- fused generate + payoff: the paths are never stored -------------------------------------------------------------
+
+@pytest.mark.parametrize("model,params,D", [
+    ("gbm_log", dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 252), 252),              # table-fused log-Euler step (C4 / C5 model)
+    ("gbm_log", dict(S0=100.0, mu=0.05, sigma=0.9, dt=0.25), 8),                    # large steps: the unfused log model
+    ("gbm_euler", dict(S0=1.0, mu=0.08, sigma=0.15, dt=1 / 100), 120),              # RP.py:65
+    ("sv", dict(S0=1.0, mu=0.03, s0=0.16679, a=0.0033281299103885727, b=0.1562947229160206, c=0.01583113545983743, dt=1 / 252), 60),
+])
+@pytest.mark.parametrize("kind", ["call", "put", "floor"])
+def test_fused_generate_and_payoff_equals_stored_paths(cuda, model, params, D, kind):
+    """orp_paths_payoff against orp_paths + orp_payoff_reduce on the same index window (start not on a tile boundary,
+    ragged count): sums to 1e-12 (another summation order), out-of-the-money counts exactly; and against the oracle's
+    NumPy payoff on the reference's path code to 1e-9."""
+    import orp_b200
+    from oracle import paths as opaths
+    start, count = 37, 70_001
+    s0 = params["S0"]
+    ks = np.array([0.8, 0.9, 1.0, 1.0, 1.1, 1.2, 0.95, 1.05, 1.0, 1.3, 0.7]) * s0
+    ts = np.array([D, D // 2, D, 1, D // 3, D, 0, D - 1, D // 2, D, D // 2])        # 3 share D // 2, 4 share D; t = 0 and t = 1
+    tm = orp_b200.simulate_paths(model, params, steps=D, start=start, count=count, device=cuda, time_major=True)
+    ref_s, ref_o = orp_b200.payoff_sums(tm, ks, ts, kind, s0=s0)
+    got_s, got_o = orp_b200.payoff_sums_fused(model, params, ks, ts, kind, steps=D, start=start, count=count, device=cuda, s0=s0)
+    np.testing.assert_allclose(got_s.cpu().numpy(), ref_s.cpu().numpy(), rtol=1e-12)
+    assert np.array_equal(got_o.cpu().numpy(), ref_o.cpu().numpy())
+    p_or = dict(params)
+    osum, ootm = opaths.payoff_sums_window({"gbm_euler": "gbm_arith"}.get(model, model), p_or, D + 1, start, count, ks, ts, kind)
+    np.testing.assert_allclose(got_s.cpu().numpy(), osum, rtol=1e-9)
+    assert np.array_equal(got_o.cpu().numpy(), ootm)
+
+
+def test_fused_sweep_c4_shape_and_errors(cuda):
+    """BASELINE C4's shape on a smaller set: 64 calls = 8 strikes x 8 maturities off one 2^18-path 252-step GBM set, from the
+    fused kernel, against the stored-path sweep (1e-12) and Black-Scholes; more than 8 strikes per maturity (several
+    groups on one step); bad arguments are ValueError."""
+    import orp_b200
+    from oracle import paths as opaths
+    p = dict(S0=100.0, mu=0.05, sigma=0.2, dt=1 / 252)
+    m, D = 18, 252
+    ks = np.repeat(np.linspace(80.0, 120.0, 8), 8)
+    ts = np.tile(np.arange(1, 9) * (D // 8) + D % 8, 8)
+    tm = orp_b200.simulate_paths("gbm_log", p, m=m, steps=D, device=cuda, time_major=True)
+    ref, _ = orp_b200.price_european(tm, ks, ts, "call", r=0.05, dt=1 / 252)
+    got, potm = orp_b200.price_european_fused("gbm_log", p, ks, ts, "call", r=0.05, m=m, steps=D, device=cuda)
+    np.testing.assert_allclose(got, ref, rtol=1e-12)
+    bs = np.array([opaths.black_scholes_call(100.0, k, t / 252, 0.05, 0.2) for k, t in zip(ks, ts)])
+    assert np.abs(got - bs).max() < 2e-2 and (potm > 0).all() and (potm < 1).all()
+    ks2, ts2 = np.linspace(60.0, 140.0, 20), np.full(20, D)                          # 20 strikes on one maturity: 3 groups
+    ref2, _ = orp_b200.price_european(tm, ks2, ts2, "put", r=0.05, dt=1 / 252)
+    got2, _ = orp_b200.price_european_fused("gbm_log", p, ks2, ts2, "put", r=0.05, m=m, steps=D, device=cuda)
+    np.testing.assert_allclose(got2, ref2, rtol=1e-12)
+    with pytest.raises(ValueError):
+        orp_b200.payoff_sums_fused("gbm_log", p, [100.0], [D + 1], m=m, steps=D, device=cuda)
+    with pytest.raises(ValueError):
+        orp_b200.payoff_sums_fused("gbm_log", p, np.full(65, 100.0), np.full(65, D), m=m, steps=D, device=cuda)
