@@ -29,22 +29,39 @@ def needs_build() -> bool:
     if not os.path.exists(LIB):
         return True
     t = os.path.getmtime(LIB)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(HERE, "..", "include", "orp_b200.h")]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h", ".inc"))]
+    deps.append(os.path.join(HERE, "..", "include", "orp_b200.h"))
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, defines=(), out: str = LIB) -> str:
+    """Compiles to a temporary name in the same directory under a file lock and renames it into place, so that several
+    ranks started together (torchrun) never load a half-written library; whoever gets the lock second finds it built."""
+    if not force and out == LIB and not needs_build():
         return LIB
-    cmd = [nvcc_path(), *NVCC_FLAGS, *(["-Xptxas", "-v"] if verbose else []),
-           *[os.path.join(CSRC, s) for s in SOURCES], "-o", LIB]
-    r = subprocess.run(cmd, capture_output=True, text=True)
-    if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
-    if verbose:
-        print(r.stderr)
-    return LIB
+    import fcntl
+    with open(out + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if not force and out == LIB and not needs_build():
+            return LIB
+        tmp = f"{out}.{os.getpid()}.tmp"
+        cmd = [nvcc_path(), *NVCC_FLAGS, *[f"-D{d}" for d in defines], *(["-Xptxas", "-v"] if verbose else []),
+               *[os.path.join(CSRC, s) for s in SOURCES], "-o", tmp]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            if os.path.exists(tmp):
+                os.remove(tmp)
+            raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
+        os.replace(tmp, out)
+        if verbose:
+            print(r.stderr)
+    return out
+
+
+def build_trace() -> str:
+    """The instrumented library of tools/trace_fit.py (phase timestamps inside the persistent fit kernel)."""
+    return build(force=True, defines=("ORP_FIT_TRACE",), out=os.path.join(HERE, "liborp_b200_trace.so"))
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_trace() if "--trace" in sys.argv else build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -929,9 +929,9 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 }
                 if (blockIdx.x < g_k) warp_partial<NET>(g, loss, n, s_red[sg][warp]);
             }
+            ORP_TRACE(1);
             __syncthreads();
             if (blockIdx.x < g_k) block_publish<NET>(s_red, n_seg, part + 2 * blockIdx.x, (size_t)kGsumLen * kLLBlocks, kLLBlocks, tag);
-            ORP_TRACE(1);
             ORP_TRACE(2);
             // the step's learning rate: Adam bias terms from a table that all threads refill together every 256 steps
             if (((barriers - 1u) & (kFitThreads - 1u)) == 0u) {

@@ -284,7 +284,8 @@ struct FusedPayoff {
     double strikes[ORP_MAX_OPTIONS];             // in group order
 };
 
-__device__ __forceinline__ void fused_group(const FusedPayoff& f, int g, double p0, double p1, bool ok0, bool ok1, int lane,
+// (not inlined: it runs at a handful of time steps per tile; inlined it bloats the step loop and its register budget)
+__device__ __noinline__ void fused_group(const FusedPayoff& f, int g, double p0, double p1, bool ok0, bool ok1, int lane,
                                             double* __restrict__ w_sum, unsigned* __restrict__ w_otm, unsigned long long* __restrict__ w_nan) {
     const int first = f.grp_first[g], n = f.grp_n[g];
     const int KIND = f.kind;                     // uniform over the launch
@@ -338,7 +339,7 @@ __device__ __forceinline__ void fused_group(const FusedPayoff& f, int g, double 
 }
 
 template <int MODEL, bool FUSED, bool TLS>
-__global__ void __launch_bounds__(kPathThreads, 1) paths_payoff_kernel(const PathArgs a, const FusedPayoff f) {
+__global__ void __launch_bounds__(kPathThreads, 1) paths_payoff_kernel(const PathArgs a, const __grid_constant__ FusedPayoff f) {
     static_assert(!FUSED || MODEL == ORP_MODEL_GBM_LOG, "only the log-Euler GBM step fuses into the table");
     extern __shared__ __align__(128) char s_tab[];
     constexpr int kWarps = kPathThreads / 32;
@@ -396,29 +397,36 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_payoff_kernel(const Pat
             uint2 tl_next = TLS ? lds_u32x2(tp_a) : __ldg(a.tlane_a + (size_t)t0 * 32 + lane);
             uint2 tb_next = make_uint2(0u, 0u);
             if (MODEL == ORP_MODEL_SV) tb_next = TLS ? lds_u32x2(tp_b) : __ldg(a.tlane_b + (size_t)t0 * 32 + lane);
-            for (int s = 0; s < nc; ++s) {
-                const int t = t0 + s;
-                const uint32_t base = __shfl_sync(kFull, bl_a, s);
-                const uint2 tl = tl_next;
-                if (TLS) { tp_a += 256u; tl_next = lds_u32x2(tp_a); }
-                else tl_next = __ldg(a.tlane_a + (size_t)min(t + 1, D) * 32 + lane);
-                if (FUSED) {
-                    s_0 *= table_eval(base ^ tl.x, tab);
-                    s_1 *= table_eval(base ^ tl.y, tab);
-                } else {
-                    const double z0 = ndtri_bits(base ^ tl.x, tab);
-                    const double z1 = ndtri_bits(base ^ tl.y, tab);
-                    double y0 = 0.0, y1 = 0.0;
-                    if (MODEL == ORP_MODEL_SV) {
-                        const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
-                        const uint2 tb = tb_next;
-                        if (TLS) { tp_b += 256u; tb_next = lds_u32x2(tp_b); }
-                        else tb_next = __ldg(a.tlane_b + (size_t)min(t + 1, D) * 32 + lane);
-                        y0 = ndtri_bits(base_b ^ tb.x, tab);
-                        y1 = ndtri_bits(base_b ^ tb.y, tab);
+            int s = 0;
+            while (s < nc) {
+                // steps up to and including the next maturity of this chunk run without a test per step
+                const int s_end = next_step >= t0 + s && next_step - t0 < nc ? next_step - t0 + 1 : nc;
+#pragma unroll 2
+                for (; s < s_end; ++s) {
+                    const int t = t0 + s;
+                    const uint32_t base = __shfl_sync(kFull, bl_a, s);
+                    const uint2 tl = tl_next;
+                    if (TLS) { tp_a += 256u; tl_next = lds_u32x2(tp_a); }
+                    else tl_next = __ldg(a.tlane_a + (size_t)min(t + 1, D) * 32 + lane);
+                    if (FUSED) {
+                        s_0 *= table_eval(base ^ tl.x, tab);
+                        s_1 *= table_eval(base ^ tl.y, tab);
+                    } else {
+                        const double z0 = ndtri_bits(base ^ tl.x, tab);
+                        const double z1 = ndtri_bits(base ^ tl.y, tab);
+                        double y0 = 0.0, y1 = 0.0;
+                        if (MODEL == ORP_MODEL_SV) {
+                            const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
+                            const uint2 tb = tb_next;
+                            if (TLS) { tp_b += 256u; tb_next = lds_u32x2(tp_b); }
+                            else tb_next = __ldg(a.tlane_b + (size_t)min(t + 1, D) * 32 + lane);
+                            y0 = ndtri_bits(base_b ^ tb.x, tab);
+                            y1 = ndtri_bits(base_b ^ tb.y, tab);
+                        }
+                        advance<MODEL, false>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
                     }
-                    advance<MODEL, false>(a, s_0, s_1, v_0, v_1, z0, z1, y0, y1);
                 }
+                const int t = t0 + s - 1;
                 if (t == next_step) {                                       // warp-uniform
                     double p0 = s_0, p1 = s_1;
                     if (!kLevel<MODEL> && !FUSED) { p0 = exp(s_0); p1 = exp(s_1); }

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """BASELINE.json configs C1..C4 end to end on one GPU (C5 is bench.py): device times (CUDA events), prices, errors.
 
-    python tools/run_configs.py > profiles/r01_configs.json
+    python tools/run_configs.py > profiles/r02_configs.json
 """
 import json
 import os
@@ -71,8 +71,16 @@ strikes = np.repeat(np.linspace(80.0, 120.0, 8), 8)
 cols = np.tile(np.arange(1, 9) * 31 + 4, 8)
 ms_sweep, (prices, p_otm) = timed(lambda: orp_b200.price_european(tm, strikes, cols, "call", r=0.05, dt=1 / 252))
 bs = np.array([opaths.black_scholes_call(100.0, k, c / 252, 0.05, 0.2) for k, c in zip(strikes, cols)])
+del tm
+# the same sweep from the fused generate + payoff kernel: no path is ever stored
+ms_fused, (fprices, _) = timed(lambda: orp_b200.price_european_fused("gbm_log", p, strikes, cols, "call", r=0.05, m=24, steps=252, device=dev),
+                               reps=5)
 out.append(dict(config="C4 strike/maturity sweep, 64 calls on one 2^24 x 252 GBM set (1 GPU)", ms_paths=ms_paths,
                 path_steps_per_s=2 ** 24 * 252 / ms_paths * 1e3, ms_sweep=ms_sweep, options_per_s=64 / ms_sweep * 1e3,
+                ms_stored_total=ms_paths + ms_sweep,
+                ms_fused_generate_payoff=ms_fused, fused_options_per_s=64 / ms_fused * 1e3,
+                fused_equivalent_path_steps_per_s=2 ** 24 * 252 / ms_fused * 1e3, fused_equivalent_GBps=2 ** 24 * 252 * 8 / ms_fused / 1e6,
+                fused_max_rel_diff_vs_stored=float(np.abs(fprices / prices - 1).max()),
                 max_abs_err_vs_black_scholes=float(np.abs(prices - bs).max()),
                 max_rel_err_vs_black_scholes=float(np.abs(prices / bs - 1).max())))
 print(json.dumps(out, indent=1))
