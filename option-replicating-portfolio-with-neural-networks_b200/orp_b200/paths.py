@@ -116,6 +116,7 @@ def simulate_paths(model: str, params: dict, m: int | None = None, steps: int | 
 
 
 _scratch = {}
+_sweep_plans = {}
 
 
 def _payoff_scratch(device, n_opt):
@@ -127,45 +128,88 @@ def _payoff_scratch(device, n_opt):
     return _scratch[key]
 
 
+def _sweep_plan(strikes, columns, n_cols, device):
+    """Host-side preparation of one (strikes, columns) set, cached: the kernel handles options in chunks of 8 and reads a
+    maturity column once per chunk it appears in, so the options are grouped by column (option 0 stays first: it owns
+    values_out) — a 64-option sweep over 8 maturities streams 8 columns instead of 64 — and a packed output buffer
+    [sums | otm | count] that is all-reduced as one vector.  Results are returned in the caller's order."""
+    torch = _lib.require_cuda()
+    strikes = np.ascontiguousarray(np.atleast_1d(strikes), dtype=np.float64)
+    columns = np.ascontiguousarray(np.atleast_1d(columns), dtype=np.int64)
+    key = (strikes.tobytes(), columns.tobytes(), int(n_cols), str(device))
+    plan = _sweep_plans.get(key)
+    if plan is None:
+        if strikes.shape != columns.shape:
+            raise ValueError("strikes and columns must have the same length")
+        n_opt = strikes.size
+        if not 1 <= n_opt <= _lib.MAX_OPTIONS:
+            raise ValueError(f"between 1 and {_lib.MAX_OPTIONS} options per call")
+        cols = np.where(columns < 0, columns + n_cols, columns).astype(np.int32)
+        if (cols < 0).any() or (cols >= n_cols).any():
+            raise ValueError("column index out of range")
+        order = np.concatenate([[0], 1 + np.argsort(cols[1:], kind="stable")]).astype(np.int64)
+        identity = np.array_equal(order, np.arange(n_opt))
+        plan = dict(n_opt=n_opt, cols=cols, strikes_s=np.ascontiguousarray(strikes[order]), cols_s=np.ascontiguousarray(cols[order]),
+                    inv=None if identity else torch.from_numpy(np.argsort(order)).to(device), inv_host=np.argsort(order),
+                    packed=torch.empty(2 * n_opt + 1, dtype=torch.float64, device=device))
+        if len(_sweep_plans) > 256:
+            _sweep_plans.clear()
+        _sweep_plans[key] = plan
+    return plan
+
+
+def _payoff_launch(paths_tm, plan, kind, s0, values_out, value_scale):
+    """Enqueues the payoff kernels of a plan: sums -> plan['packed'][:n], otm -> [n:2n], in the plan's (grouped) order."""
+    torch = _lib.require_cuda()
+    if kind not in _lib.PAYOFF:
+        raise ValueError(f"kind must be one of {sorted(_lib.PAYOFF)}")
+    if not paths_tm.is_contiguous():
+        raise ValueError("paths_tm must be the contiguous time-major tensor")
+    n_cols, count = paths_tm.shape
+    n_opt, packed = plan["n_opt"], plan["packed"]
+    dt = _lib.F64 if paths_tm.dtype == torch.float64 else _lib.F32
+    with torch.cuda.device(paths_tm.device):
+        _lib.check(_lib.lib().orp_payoff_reduce(
+            _lib.ptr(paths_tm), dt, count, count, _lib.PAYOFF[kind], n_opt, _lib.ptr(plan["strikes_s"]), _lib.ptr(plan["cols_s"]),
+            int(n_cols), float(s0), float(value_scale), _lib.ptr(values_out), _lib.ptr(packed), _lib.ptr(packed) + 8 * n_opt,
+            _lib.ptr(_payoff_scratch(paths_tm.device, n_opt)), _lib.stream_ptr()))
+
+
 def payoff_sums(paths_tm, strikes, columns, kind: str = "call", s0: float = 0.0,
                 values_out=None, value_scale: float = 1.0):
     """Per option ``j``: ``sum_i payoff(S[columns[j]][i], strikes[j])`` and the out-of-the-money count, as
     two fp64 CUDA tensors of length ``n_opt`` (no host sync).  ``paths_tm`` is the TIME-MAJOR
     ``(n_cols, count)`` tensor.  ``values_out`` (fp32, ``count``) receives option 0's payoff times
     ``value_scale`` — ``values[:, -1]`` of the backward loop."""
-    torch = _lib.require_cuda()
-    if kind not in _lib.PAYOFF:
-        raise ValueError(f"kind must be one of {sorted(_lib.PAYOFF)}")
-    strikes = np.ascontiguousarray(np.atleast_1d(strikes), dtype=np.float64)
-    columns = np.ascontiguousarray(np.atleast_1d(columns), dtype=np.int32)
-    if strikes.shape != columns.shape:
-        raise ValueError("strikes and columns must have the same length")
-    n_opt = strikes.size
-    if not 1 <= n_opt <= _lib.MAX_OPTIONS:
-        raise ValueError(f"between 1 and {_lib.MAX_OPTIONS} options per call")
-    n_cols, count = paths_tm.shape
-    columns = np.where(columns < 0, columns + n_cols, columns).astype(np.int32)
-    if (columns < 0).any() or (columns >= n_cols).any():
-        raise ValueError("column index out of range")
-    if not paths_tm.is_contiguous():
-        raise ValueError("paths_tm must be the contiguous time-major tensor")
-    dt = _lib.F64 if paths_tm.dtype == torch.float64 else _lib.F32
-    # The kernel handles options in chunks of 8 and reads a maturity column once per chunk it appears in: group the
-    # options by column (option 0 stays first: it owns values_out) so a 64-option sweep over 8 maturities streams 8
-    # columns instead of 64.  Results are returned in the caller's order.
-    order = np.concatenate([[0], 1 + np.argsort(columns[1:], kind="stable")]).astype(np.int64)
-    strikes_s, columns_s = np.ascontiguousarray(strikes[order]), np.ascontiguousarray(columns[order])
-    with torch.cuda.device(paths_tm.device):
-        sums = torch.empty(n_opt, dtype=torch.float64, device=paths_tm.device)
-        otm = torch.empty(n_opt, dtype=torch.float64, device=paths_tm.device)
-        _lib.check(_lib.lib().orp_payoff_reduce(
-            _lib.ptr(paths_tm), dt, count, count, _lib.PAYOFF[kind], n_opt, _lib.ptr(strikes_s), _lib.ptr(columns_s),
-            int(n_cols), float(s0), float(value_scale), _lib.ptr(values_out), _lib.ptr(sums), _lib.ptr(otm),
-            _lib.ptr(_payoff_scratch(paths_tm.device, n_opt)), _lib.stream_ptr()))
-        if n_opt > 1 and not np.array_equal(order, np.arange(n_opt)):
-            inv = torch.from_numpy(np.argsort(order)).to(paths_tm.device)
-            sums, otm = sums[inv], otm[inv]
+    plan = _sweep_plan(strikes, columns, paths_tm.shape[0], paths_tm.device)
+    _payoff_launch(paths_tm, plan, kind, s0, values_out, value_scale)
+    n = plan["n_opt"]
+    out = plan["packed"][:2 * n].clone()                    # the plan's buffer is overwritten by the next call
+    sums, otm = out[:n], out[n:]
+    if plan["inv"] is not None:
+        sums, otm = sums[plan["inv"]], otm[plan["inv"]]
     return sums, otm
+
+
+def price_european(paths, strikes, maturities_idx, kind: str = "call", r: float = 0.0, dt: float = 1.0,
+                   total_paths: int | None = None, group=None):
+    """Discounted Monte-Carlo prices ``exp(-r * t_col) * mean(payoff)`` for up to 64 (strike, maturity
+    column) pairs sharing one path set.  ``paths`` is what :func:`simulate_paths` returned (either
+    orientation).  ``dt`` is the spacing of the KEPT columns.  With ``torch.distributed`` initialised (or
+    ``group`` given) the packed sums are all-reduced over ranks — ONE collective per call, into a buffer that lives with
+    the cached option set, so a repeated sweep allocates nothing.  Returns ``(prices, prob_otm)`` NumPy arrays."""
+    tm = paths if paths.is_contiguous() else paths.t()
+    plan = _sweep_plan(strikes, maturities_idx, tm.shape[0], tm.device)
+    _payoff_launch(tm, plan, kind, 0.0, None, 1.0)
+    k, packed = plan["n_opt"], plan["packed"]
+    packed[2 * k] = float(tm.shape[1])
+    from .dist import allreduce_sum_
+    allreduce_sum_(packed, group)
+    host = packed.cpu().numpy()
+    total = host[-1] if total_paths is None else float(total_paths)
+    inv = plan["inv_host"]
+    disc = np.exp(-r * dt * plan["cols"])
+    return disc * host[:k][inv] / total, host[k:2 * k][inv] / total
 
 
 def _path_params(model, params, steps, ordering, dtype, keep_every, engine_dim):
@@ -264,23 +308,3 @@ def price_european_fused(model: str, params: dict, strikes, maturity_steps, kind
     return disc * packed[:k] / total, packed[k:2 * k] / total
 
 
-def price_european(paths, strikes, maturities_idx, kind: str = "call", r: float = 0.0, dt: float = 1.0,
-                   total_paths: int | None = None, group=None):
-    """Discounted Monte-Carlo prices ``exp(-r * t_col) * mean(payoff)`` for up to 64 (strike, maturity
-    column) pairs sharing one path set.  ``paths`` is what :func:`simulate_paths` returned (either
-    orientation).  ``dt`` is the spacing of the KEPT columns.  With ``torch.distributed`` initialised (or
-    ``group`` given) the sums are all-reduced over ranks.  Returns ``(prices, prob_otm)`` NumPy arrays."""
-    torch = _lib.require_cuda()
-    tm = paths if paths.is_contiguous() else paths.t()
-    sums, otm = payoff_sums(tm, strikes, maturities_idx, kind)
-    n = tm.shape[1]
-    from .dist import allreduce_sum_
-    packed = torch.cat([sums, otm, torch.tensor([float(n)], dtype=torch.float64, device=sums.device)])
-    allreduce_sum_(packed, group)
-    packed = packed.cpu().numpy()
-    k = len(sums)
-    total = packed[-1] if total_paths is None else float(total_paths)
-    cols = np.atleast_1d(np.asarray(maturities_idx))
-    cols = np.where(cols < 0, cols + tm.shape[0], cols)
-    disc = np.exp(-r * dt * cols)
-    return disc * packed[:k] / total, packed[k:2 * k] / total
