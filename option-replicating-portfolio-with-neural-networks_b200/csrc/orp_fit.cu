@@ -318,6 +318,7 @@ struct FitArgs {
     float inv_scale_f; double inv_scale; float b_t, b_t1;
     int skip;                  // non-zero: samples with a non-finite input or target take no part (ORP_FIT_SKIP_NONFINITE)
     int n_seg;                 // the batch is n_seg segments of `count` samples, segment v starting seg_stride * v samples in
+    int g_blocks;              // virtual blocks per segment (fit_blocks(count)): part of the sums' definition, not of the launch
     uint64_t seg_stride;
 };
 
@@ -461,7 +462,7 @@ constexpr int kMaxSeg = ORP_FIT_MAX_SEGMENTS;
 __device__ __forceinline__ void reduce_partials(const double* __restrict__ partials, int n_blocks, int n_seg,
                                                 double* __restrict__ gsum, double* s_copy) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int k = warp; k < kGsumLen; k += 8) {
+    for (int k = warp; k < kGsumLen; k += (int)(blockDim.x >> 5)) {
         double seg[kMaxSeg];
 #pragma unroll
         for (int v = 0; v < kMaxSeg; ++v) {
@@ -478,7 +479,10 @@ __device__ __forceinline__ void reduce_partials(const double* __restrict__ parti
     }
 }
 
-constexpr int kFitThreads = 256;
+#ifndef ORP_FIT_THREADS
+#define ORP_FIT_THREADS 256
+#endif
+constexpr int kFitThreads = ORP_FIT_THREADS;       // scaled drivers, predict and residual kernels
 constexpr int kGsum = kGsumLen;
 
 // Sum over the 32 lanes of a warp of N per-lane values, as a reduce-scatter: at every stage a lane keeps one half
@@ -557,23 +561,29 @@ __device__ __forceinline__ void warp_partial(const Grads<NET>& g, float loss, ui
     }
 }
 
-// Block totals of the n_seg units of a step as fp64 vectors: for every (segment, column) the warps' totals are added in
-// warp order and written to dst[(segment * seg_stride + index * stride)] (index = k for the gradient of parameter k,
+// Block totals of the units this block worked on in a step, as fp64 vectors.  A UNIT is (segment sv, virtual block vb):
+// virtual block vb of g_k takes the tiles vb, vb + g_k, ... of the segment's part, whatever physical block runs it — the
+// units of a step are numbered u = sv * g_k + vb and physical block b of G runs u = b, b + G, ... (slot 0, 1, ...), so a
+// step of few tiles per segment still spreads over the whole grid, and the sums do not depend on the grid at all.
+// For every (slot, column) the warps' totals are added in warp order and written to
+// dst[sv * seg_stride + index * col_stride + vb * blk_stride] (index = k for the gradient of parameter k,
 // ORP_FIT_MAX_PARAMS for the loss, + 1 for the count).  Call after a block barrier that follows the last warp_partial.
 // Shared by every scaled driver of the fit, so they agree bit for bit.
 // tag != 0: every entry is written as two 8-byte words {low half, tag}, {high half, tag} (dst counts 16-byte
 // entries), so that a reader polling for `tag` needs no barrier and no fence (8-byte accesses are single-copy atomic).
 template <int NET>
-__device__ __forceinline__ void block_publish(const float (&s_red)[kMaxSeg][kFitThreads / 32][Net<NET>::P + 2], int n_seg,
-                                              double* __restrict__ dst, size_t seg_stride, size_t stride, unsigned int tag = 0u) {
+__device__ __forceinline__ void block_publish(const float (&s_red)[kMaxSeg][kFitThreads / 32][Net<NET>::P + 2], int n_slots,
+                                              uint32_t u0, uint32_t u_stride, uint32_t g_k, double* __restrict__ dst,
+                                              size_t seg_stride, size_t col_stride, size_t blk_stride, unsigned int tag = 0u) {
     constexpr int P = Net<NET>::P;
     constexpr int N = P + 2;
-    for (int item = threadIdx.x; item < n_seg * N; item += kFitThreads) {
-        const int sv = item / N, q = item - sv * N;
+    for (int item = threadIdx.x; item < n_slots * N; item += kFitThreads) {
+        const int slot = item / N, q = item - slot * N;
+        const uint32_t u = u0 + (uint32_t)slot * u_stride, sv = u / g_k, vb = u - sv * g_k;
         double t = 0.0;
 #pragma unroll
-        for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[sv][w][q];
-        const size_t at = (size_t)sv * seg_stride + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * stride;
+        for (int w = 0; w < kFitThreads / 32; ++w) t += (double)s_red[slot][w][q];
+        const size_t at = (size_t)sv * seg_stride + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * col_stride + (size_t)vb * blk_stride;
         if (tag) st_tagged(dst + 2 * at, t, tag); else dst[at] = t;
     }
 }
@@ -705,20 +715,22 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
     __syncthreads();
     const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
 
-    RawSample<NET, T> first[kFitUnroll<NET>];
-    load_first_tile<NET, T>(seg_args<T>(a, 0), blockIdx.x, first);
+    // one UNIT per block: block b works on virtual block b % g_k of segment b / g_k (g_k = a.g_blocks blocks per segment)
     __shared__ float s_red[kMaxSeg][kFitThreads / 32][N::P + 2];
-    for (int v = 0; v < a.n_seg; ++v) {                   // one UNIT (fp32 accumulators of this block) per segment
+    const uint32_t g_k = (uint32_t)a.g_blocks, sv = blockIdx.x / g_k, vb = blockIdx.x - sv * g_k;
+    {
+        const FitArgs av = seg_args<T>(a, (int)sv);
+        RawSample<NET, T> first[kFitUnroll<NET>];
+        load_first_tile<NET, T>(av, vb, first);
         Grads<NET> g;
         g.zero();
         float loss = 0.f;
         uint32_t n = 0;
-        accumulate_tiles<NET, LOSS, T, SKIP>(seg_args<T>(a, v), s_wa, blockIdx.x, gridDim.x, first, g, loss, n);
-        if (v + 1 < a.n_seg) load_first_tile<NET, T>(seg_args<T>(a, v + 1), blockIdx.x, first);
-        warp_partial<NET>(g, loss, n, s_red[v][threadIdx.x >> 5]);
+        accumulate_tiles<NET, LOSS, T, SKIP>(av, s_wa, vb, g_k, first, g, loss, n);
+        warp_partial<NET>(g, loss, n, s_red[0][threadIdx.x >> 5]);
     }
     __syncthreads();
-    block_publish<NET>(s_red, a.n_seg, partials + (size_t)blockIdx.x * kGsum, (size_t)gridDim.x * kGsum, 1);
+    block_publish<NET>(s_red, 1, blockIdx.x, 0u, g_k, partials, (size_t)g_k * kGsum, 1, kGsum);
     if (STEP) {
         __shared__ bool s_last;
         __shared__ double s_g[kGsumLen];
@@ -729,7 +741,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
         __syncthreads();
         if (!s_last) return;
         __threadfence();
-        reduce_partials(partials, (int)gridDim.x, a.n_seg, gsum, s_g);
+        reduce_partials(partials, a.g_blocks, a.n_seg, gsum, s_g);
         __syncthreads();
         optimiser_step(N::P, params, state, s_g, flags);
         if (threadIdx.x == 0) *ticket = 0u;                // ready for the next launch
@@ -851,7 +863,7 @@ __device__ __forceinline__ FitArgs part_args(const RunArgs& r, int v, int k, uin
     if (r.a.feat2) a.feat2 = r.a.feat2 + off;
     const uint64_t tile = (uint64_t)kFitThreads * (r.unroll);
     const uint64_t want = (a.count + tile - 1) / tile;
-    g_k = (uint32_t)min(want, (uint64_t)min((uint32_t)r.max_blocks_per_part, G));
+    g_k = (uint32_t)min(want, (uint64_t)r.max_blocks_per_part);      // = fit_blocks(a.count): no function of the grid
     return a;
 }
 
@@ -868,7 +880,8 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     __shared__ float s_red[kMaxSeg][kFitThreads / 32][P + 2];
     __shared__ float s_lr_t;
     __shared__ int s_improved;
-    __shared__ double s_num[kFitThreads], s_den[kFitThreads];      // Adam bias terms of the next 256 steps
+    constexpr int kLrTable = 256;
+    __shared__ double s_num[kLrTable], s_den[kLrTable];            // Adam bias terms of the next 256 steps
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned int* abort_flag = reinterpret_cast<unsigned int*>(state + ST_ABORT);
 
@@ -892,9 +905,11 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
 
     RawSample<NET, T> first[kFitUnroll<NET>];
     {
-        uint32_t g0;
-        const FitArgs a0 = part_args<T>(r, 0, 0, G, g0);
-        load_first_tile<NET, T>(a0, blockIdx.x, first);
+        uint32_t g0, g_same;
+        part_args<T>(r, 0, 0, G, g0);
+        const uint32_t sg0 = blockIdx.x / g0;
+        for (int u = 0; u < kFitUnroll<NET>; ++u) first[u] = RawSample<NET, T>{};
+        if (sg0 < (uint32_t)r.a.n_seg) load_first_tile<NET, T>(part_args<T>(r, (int)sg0, 0, G, g_same), blockIdx.x - sg0 * g0, first);
     }
     for (int e = 0; e < r.n_epochs && alive; ++e) {
         if (s_c[ST_STOP] != 0.0) break;                                    // same value in every block
@@ -912,29 +927,38 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             const int n_seg = r.a.n_seg;
             double* const part = ll_part + (size_t)par * kMaxSeg * kGsumLen * kLLBlocks * 2;
             uint32_t g_k = 0;
-            for (int sg = 0; sg < n_seg; ++sg) {
-                const FitArgs a = part_args<T>(r, sg, k, G, g_k);
+            part_args<T>(r, 0, k, G, g_k);                                     // virtual blocks per segment in this part
+            const uint32_t n_units = (uint32_t)n_seg * g_k;
+            int n_slots = 0;
+            for (uint32_t u = blockIdx.x; u < n_units; u += G, ++n_slots) {
+                const uint32_t sg = u / g_k, vb = u - sg * g_k;
+                uint32_t g_same;
+                const FitArgs a = part_args<T>(r, (int)sg, k, G, g_same);
                 Grads<NET> g;
                 g.zero();
                 float loss = 0.f;
                 uint32_t n = 0;
-                if (blockIdx.x < g_k) accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, blockIdx.x, g_k, first, g, loss, n);
-                // request the first tile of the NEXT unit now (next segment, or part k + 1 of segment 0: those loads land
-                // while this block waits for the other blocks' totals; wasted only when the fit stops here)
-                {
+                accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, vb, g_k, first, g, loss, n);
+                // request the first tile of this block's NEXT unit now (in this step, or its first unit of the next step:
+                // those loads land while this block waits for the other blocks' totals; wasted only when the fit stops here)
+                if (u + G < n_units) {
+                    const uint32_t sg2 = (u + G) / g_k;
+                    load_first_tile<NET, T>(part_args<T>(r, (int)sg2, k, G, g_same), u + G - sg2 * g_k, first);
+                } else {
                     uint32_t g_next;
-                    const bool same_step = sg + 1 < n_seg;
-                    const FitArgs a_next = part_args<T>(r, same_step ? sg + 1 : 0, same_step ? k : (k + 1 < r.n_parts ? k + 1 : 0), G, g_next);
-                    load_first_tile<NET, T>(a_next, blockIdx.x, first);
+                    const int k2 = k + 1 < r.n_parts ? k + 1 : 0;
+                    part_args<T>(r, 0, k2, G, g_next);
+                    const uint32_t sg2 = blockIdx.x / g_next;
+                    if (sg2 < (uint32_t)n_seg) load_first_tile<NET, T>(part_args<T>(r, (int)sg2, k2, G, g_same), blockIdx.x - sg2 * g_next, first);
                 }
-                if (blockIdx.x < g_k) warp_partial<NET>(g, loss, n, s_red[sg][warp]);
+                warp_partial<NET>(g, loss, n, s_red[n_slots][warp]);
             }
             ORP_TRACE(1);
             __syncthreads();
-            if (blockIdx.x < g_k) block_publish<NET>(s_red, n_seg, part + 2 * blockIdx.x, (size_t)kGsumLen * kLLBlocks, kLLBlocks, tag);
+            block_publish<NET>(s_red, n_slots, blockIdx.x, G, g_k, part, (size_t)kGsumLen * kLLBlocks, kLLBlocks, 1, tag);
             ORP_TRACE(2);
             // the step's learning rate: Adam bias terms from a table that all threads refill together every 256 steps
-            if (((barriers - 1u) & (kFitThreads - 1u)) == 0u) {
+            if (((barriers - 1u) & (kLrTable - 1u)) == 0u && tid < kLrTable) {
                 const double ti = s_c[ST_ADAM_T] + 1.0 + (double)tid;
                 s_num[tid] = sqrt(1.0 - pow(0.999, ti));
                 s_den[tid] = 1.0 - pow(0.9, ti);
@@ -946,7 +970,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 if (k == 0 && s_c[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)s_c[ST_EPOCH], lr);
                 s_c[ST_LR] = lr;
                 s_c[ST_ADAM_T] = s_c[ST_ADAM_T] + 1.0;
-                const unsigned int i = (barriers - 1u) & (kFitThreads - 1u);
+                const unsigned int i = (barriers - 1u) & (kLrTable - 1u);
                 s_lr_t = (float)(lr * s_num[i] / s_den[i]);
             }
             ORP_TRACE(3);
@@ -1346,6 +1370,7 @@ static int make_args(const orp_fit_batch* b, FitArgs& a, bool need_target) {
                 "fp32 price columns must be in network units already (inv_scale = 1): convert with orp_fit_scale_column");
     a.skip = (b->reserved & ORP_FIT_SKIP_NONFINITE) ? 1 : 0;
     a.n_seg = b->n_seg ? (int)b->n_seg : 1;
+    a.g_blocks = 1;
     a.seg_stride = b->seg_stride;
     ORP_REQUIRE(a.n_seg >= 1 && a.n_seg <= ORP_FIT_MAX_SEGMENTS, "n_seg must be in [1, %d]", ORP_FIT_MAX_SEGMENTS);
     ORP_REQUIRE(a.n_seg == 1 || a.seg_stride >= a.count, "seg_stride must be >= count (segments may not overlap)");
@@ -1381,7 +1406,8 @@ extern "C" int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const
     if (rc) return rc;
     ORP_REQUIRE(d_params && d_state && d_gsum && d_scratch, "null pointer");
     cudaStream_t st = (cudaStream_t)stream;
-    const int grid = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
+    a.g_blocks = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
+    const int grid = a.n_seg * a.g_blocks;                     // one block per unit (segment, virtual block)
     double* partials = reinterpret_cast<double*>(d_scratch);
 #define CALL_GRAD(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, false, false><<<grid, kFitThreads, 0, st>>>(a, const_cast<float*>(d_params), const_cast<double*>(d_state), partials, d_gsum, 0)
 #define CALL_GRAD_SKIP(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, false, true><<<grid, kFitThreads, 0, st>>>(a, const_cast<float*>(d_params), const_cast<double*>(d_state), partials, d_gsum, 0)
@@ -1389,7 +1415,7 @@ extern "C" int orp_fit_grad(const orp_fit_batch* b, const float* d_params, const
 #undef CALL_GRAD
 #undef CALL_GRAD_SKIP
     ORP_LAUNCH_CHECK("fit_grad_kernel");
-    fit_reduce_kernel<<<1, 256, 0, st>>>(partials, grid, a.n_seg, d_state, d_gsum);
+    fit_reduce_kernel<<<1, 256, 0, st>>>(partials, a.g_blocks, a.n_seg, d_state, d_gsum);
     ORP_LAUNCH_CHECK("fit_reduce_kernel");
     return ORP_OK;
 }
@@ -1399,7 +1425,8 @@ static int fit_step_launch(const orp_fit_batch* b, float* d_params, double* d_st
     FitArgs a;
     int rc = make_args(b, a, true);
     if (rc) return rc;
-    const int grid = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
+    a.g_blocks = fit_blocks(a.count, b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>);
+    const int grid = a.n_seg * a.g_blocks;
     double* partials = reinterpret_cast<double*>(d_scratch);
 #define CALL_STEP(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, true, false><<<grid, kFitThreads, 0, st>>>(a, d_params, d_state, partials, d_gsum, flags)
 #define CALL_STEP_SKIP(NET, LOSS, T) fit_grad_kernel<NET, LOSS, T, true, true><<<grid, kFitThreads, 0, st>>>(a, d_params, d_state, partials, d_gsum, flags)
@@ -1446,7 +1473,10 @@ static int fit_run_launch(const orp_fit_batch* b, int n_parts, float* d_params, 
     const int unroll = b->net == ORP_NET_EO ? kFitUnroll<ORP_NET_EO> : kFitUnroll<ORP_NET_RP>;
     r.unroll = unroll;
     r.max_blocks_per_part = fit_blocks(r.per, unroll);
-    const int grid = r.max_blocks_per_part;            // <= one block per SM: all blocks are co-resident
+    r.a.g_blocks = r.max_blocks_per_part;
+    // the units (segment, virtual block) of a step are dealt round-robin to the grid: at most one block per SM, all co-resident
+    int grid = r.a.n_seg * r.max_blocks_per_part;
+    if (grid > sm_count()) grid = sm_count();
     double* partials = reinterpret_cast<double*>(d_scratch);
     void* args[] = {(void*)&r, (void*)&d_params, (void*)&d_state, (void*)&partials, (void*)&d_gsum};
     const void* fn = nullptr;
