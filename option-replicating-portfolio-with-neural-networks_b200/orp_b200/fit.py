@@ -3,9 +3,10 @@
 Mirrors the loop ``for t_i in trange(n_time_steps-2, -1, -1)`` of ``Replicating_Portfolio.py:193-227`` and
 ``European Options.ipynb`` cell 13 with the Keras semantics of SURVEY.md Appendix B.  Two modes:
 
-* ``mode='scaled'`` (B200-native): one optimiser step per pass over ALL paths of all ranks — the fused
-  forward/backward kernel fills every SM, the ``[gradient, loss, count]`` vector is all-reduced over ranks,
-  Adam / LR schedule / early stopping run on the device so epochs are enqueued without host syncs.
+* ``mode='scaled'`` (B200-native): ``steps_per_epoch`` (default 8, the notebook's own 4096 / 512) optimiser steps per
+  pass over the paths, each on 1/8 of ALL paths of all ranks — the fused forward/backward kernel fills every SM, the
+  ``[gradient, loss, count]`` vectors of the ranks are exchanged inside the persistent kernel (or summed by a collective
+  in the two-stage form), Adam / LR schedule / early stopping run on the device: one launch per ``Model.fit``.
 * ``mode='keras'``: batch_size-512 mini-batches in a shuffled order, serial by definition, one thread block.
 
 Weights, both Adam states and the learning rate persist across time steps exactly as the reference's

@@ -114,8 +114,8 @@ def fit(params: torch.Tensor, opt: AdamState, net: str, x, prices, y, *, epochs:
         shuffle_rng=None, perm_fn=None):
     """One Keras ``model.fit`` call (``Replicating_Portfolio.py:211``), in place on ``params``.
 
-    ``batch_size=None`` is the scaled mode of the CUDA path: one full-batch Adam step per epoch,
-    no shuffle.  Returns ``dict(epochs_run, losses, stopped_early)``.
+    ``batch_size=None`` is one full-batch Adam step per epoch, no shuffle; the scaled mode of the CUDA path
+    (default: 8 index-order steps per epoch) is ``batch_size=n // 8`` with ``shuffle_rng=None``.  Returns ``dict(epochs_run, losses, stopped_early)``.
     EarlyStopping(monitor='loss', min_delta=0, restore_best_weights=True) as in TF 2.x: the wait
     counter is bumped first and reset on improvement; the best weights come back only when the
     stop fired before the last epoch."""
