@@ -588,6 +588,28 @@ __device__ __forceinline__ void block_publish(const float (&s_red)[kMaxSeg][kFit
     }
 }
 
+// The same for ONE unit by ONE warp (the persistent kernel publishes a unit as soon as every warp has parked its totals,
+// one unit behind the arithmetic, instead of all units in a burst at the end of the step).
+template <int NET>
+__device__ __forceinline__ void warp_publish(const float (&red)[kFitThreads / 32][Net<NET>::P + 2], uint32_t u, uint32_t g_k,
+                                             double* __restrict__ dst, size_t seg_stride, size_t col_stride, unsigned int tag, int lane) {
+    constexpr int P = Net<NET>::P;
+    constexpr int N = P + 2;
+    const uint32_t sv = u / g_k, vb = u - sv * g_k;
+    for (int q = lane; q < N; q += 32) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < kFitThreads / 32; ++w) t += (double)red[w][q];
+        const size_t at = (size_t)sv * seg_stride + (size_t)(q < P ? q : ORP_FIT_MAX_PARAMS + (q - P)) * col_stride + (size_t)vb;
+        st_tagged(dst + 2 * at, t, tag);
+    }
+}
+
+// Split block barrier on a numbered hardware barrier (PTX producer / consumer pattern): the producers' shared-memory
+// stores before bar.arrive are visible to the consumer after its bar.sync on the same barrier.
+__device__ __forceinline__ void bar_arrive(int id, int n_threads) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n_threads) : "memory"); }
+__device__ __forceinline__ void bar_sync(int id, int n_threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n_threads) : "memory"); }
+
 // Raw inputs of one sample, as loaded (conversion to the network's fp32 happens when the sample is used).
 template <int NET, typename T> struct RawSample {
     T s_t, s_t1;
@@ -661,9 +683,13 @@ __device__ __forceinline__ void load_first_tile(const FitArgs& a, uint32_t block
 
 // Forward + backward over this block's tiles of one batch: block `block` of `n_blocks` takes tiles block,
 // block + n_blocks, ...  `cur` holds the first tile (load_first_tile).  Adds into g / loss / n.
+// `nx` (optional): the batch this block works on NEXT, as virtual block `block_nx` — its first tile is requested
+// before the arithmetic of THIS batch's last tile and left in `cur`, so that a unit boundary exposes no memory latency
+// (requested only after the last tile, every boundary cost ~1.2 us: 8 % of a one-GPU step with eight units).
 template <int NET, int LOSS, typename T, bool SKIP>
 __device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa, uint32_t block, uint32_t n_blocks,
-                                                 RawSample<NET, T> (&cur)[kFitUnroll<NET>], Grads<NET>& g, float& loss, uint32_t& n) {
+                                                 RawSample<NET, T> (&cur)[kFitUnroll<NET>], Grads<NET>& g, float& loss, uint32_t& n,
+                                                 const FitArgs& nx, uint32_t block_nx, bool has_nx) {
     using N = Net<NET>;
     constexpr int U = kFitUnroll<NET>, S = kFitS;
     static_assert(U % S == 0, "tile slots are consumed S at a time");
@@ -672,10 +698,16 @@ __device__ __forceinline__ void accumulate_tiles(const FitArgs& a, uint32_t s_wa
     RawSample<NET, T> nxt[U];
     for (; base < a.count + threadIdx.x; base += stride) {        // block-uniform trip count (base - threadIdx.x < count)
         const uint64_t nb = base + stride;
+        // one load path for both cases (block-uniform choice): the next tile of this batch, or the first tile of the next one
+        const bool more = nb < a.count + threadIdx.x;
+        FitArgs src = a;
+        if (!more) { src.s_t = nx.s_t; src.s_t1 = nx.s_t1; src.target = nx.target; src.feat1 = nx.feat1; src.feat2 = nx.feat2; }
+        const uint64_t nidx = more ? nb : (uint64_t)block_nx * tile + threadIdx.x;
+        const uint64_t ncount = more ? a.count : (has_nx ? nx.count : 0ull);
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             nxt[u] = RawSample<NET, T>{};
-            if (nb + (uint64_t)u * kFitThreads < a.count) load_raw<NET, T>(a, nb + (uint64_t)u * kFitThreads, nxt[u]);
+            if (nidx + (uint64_t)u * kFitThreads < ncount) load_raw<NET, T>(src, nidx + (uint64_t)u * kFitThreads, nxt[u]);
         }
 #pragma unroll
         for (int u = 0; u < U; u += S) {
@@ -726,7 +758,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
         g.zero();
         float loss = 0.f;
         uint32_t n = 0;
-        accumulate_tiles<NET, LOSS, T, SKIP>(av, s_wa, vb, g_k, first, g, loss, n);
+        accumulate_tiles<NET, LOSS, T, SKIP>(av, s_wa, vb, g_k, first, g, loss, n, av, 0u, false);
         warp_partial<NET>(g, loss, n, s_red[0][threadIdx.x >> 5]);
     }
     __syncthreads();
@@ -938,24 +970,43 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 g.zero();
                 float loss = 0.f;
                 uint32_t n = 0;
-                accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, vb, g_k, first, g, loss, n);
-                // request the first tile of this block's NEXT unit now (in this step, or its first unit of the next step:
-                // those loads land while this block waits for the other blocks' totals; wasted only when the fit stops here)
+                // this block's NEXT unit (in this step, or its first unit of the next step): accumulate_tiles requests its first
+                // tile before the arithmetic of this unit's last tile (wasted only when the fit stops here)
+                FitArgs a_nx;
+                uint32_t vb_nx = 0u;
+                bool has_nx = true;
                 if (u + G < n_units) {
                     const uint32_t sg2 = (u + G) / g_k;
-                    load_first_tile<NET, T>(part_args<T>(r, (int)sg2, k, G, g_same), u + G - sg2 * g_k, first);
+                    a_nx = part_args<T>(r, (int)sg2, k, G, g_same);
+                    vb_nx = u + G - sg2 * g_k;
                 } else {
                     uint32_t g_next;
                     const int k2 = k + 1 < r.n_parts ? k + 1 : 0;
                     part_args<T>(r, 0, k2, G, g_next);
                     const uint32_t sg2 = blockIdx.x / g_next;
-                    if (sg2 < (uint32_t)n_seg) load_first_tile<NET, T>(part_args<T>(r, (int)sg2, k2, G, g_same), blockIdx.x - sg2 * g_next, first);
+                    has_nx = sg2 < (uint32_t)n_seg;
+                    a_nx = part_args<T>(r, has_nx ? (int)sg2 : 0, k2, G, g_same);
+                    vb_nx = blockIdx.x - sg2 * g_next;
                 }
+                accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, vb, g_k, first, g, loss, n, a_nx, vb_nx, has_nx);
                 warp_partial<NET>(g, loss, n, s_red[n_slots][warp]);
+                static_assert(kFitThreads == 256 && kMaxSeg <= 15, "eight warps take turns as publishers; barriers 1 .. kMaxSeg");
+                // hand-over inside the block, one unit behind: warp (slot mod 8) publishes unit `slot` once the other seven
+                // have parked its totals (numbered barrier slot + 1: they arrive without waiting, the publisher waits) —
+                // it does so after its OWN next unit, so the wait is over before it starts and the stores of all but the
+                // last unit are in L2 long before the owners look for them
+                if (n_slots > 0 && warp == ((n_slots - 1) & 7)) {
+                    bar_sync(n_slots, kFitThreads);
+                    warp_publish<NET>(s_red[n_slots - 1], u - G, g_k, part, (size_t)kGsumLen * kLLBlocks, kLLBlocks, tag, lane);
+                }
+                if (warp != (n_slots & 7)) bar_arrive(n_slots + 1, kFitThreads);
             }
             ORP_TRACE(1);
-            __syncthreads();
-            block_publish<NET>(s_red, n_slots, blockIdx.x, G, g_k, part, (size_t)kGsumLen * kLLBlocks, kLLBlocks, 1, tag);
+            if (n_slots > 0 && warp == ((n_slots - 1) & 7)) {                  // the last unit of the step
+                bar_sync(n_slots, kFitThreads);
+                warp_publish<NET>(s_red[n_slots - 1], blockIdx.x + (uint32_t)(n_slots - 1) * G, g_k, part, (size_t)kGsumLen * kLLBlocks,
+                                  kLLBlocks, tag, lane);
+            }
             ORP_TRACE(2);
             // the step's learning rate: Adam bias terms from a table that all threads refill together every 256 steps
             if (((barriers - 1u) & (kLrTable - 1u)) == 0u && tid < kLrTable) {

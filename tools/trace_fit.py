@@ -3,7 +3,7 @@
 the in-kernel peer exchange (2^m paths in total, 8 virtual shards).  Needs the instrumented build:
 
     python option-replicating-portfolio-with-neural-networks_b200/build.py --trace
-    ORP_B200_LIB=$PWD/option-replicating-portfolio-with-neural-networks_b200/liborp_b200_trace.so python tools/trace_fit.py [m] [parts]
+    ORP_B200_LIB=$PWD/option-replicating-portfolio-with-neural-networks_b200/liborp_b200_trace.so python tools/trace_fit.py [m] [parts] [segments]
     ORP_B200_LIB=... python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 tools/trace_fit.py 26 8
 
 Blocks 0 and G-1 of every rank write %globaltimer at eight points of each of the first 512 optimiser steps; rank 0
@@ -32,7 +32,7 @@ vals = torch.empty(tm.shape[1], dtype=torch.float32, device=dev)
 orp_b200.payoff_sums(tm, [100.0], [-1], "call", values_out=vals, value_scale=0.01)
 mdl = ReplicationNet("eo", init_params("eo", 1, 0.1), dev, peer_exchange=True if world == 1 else None)
 opt = Optimizer(dev)
-segs = virtual_segments(tm.shape[1], None, 8)
+segs = int(sys.argv[3]) if len(sys.argv) > 3 else virtual_segments(tm.shape[1], None, 8)
 b = mdl.batch(scale_column(tm[1], 0.01), scale_column(tm[2], 0.01), vals, 1.0, 0.01, 0.01, segments=segs)
 for rep in range(2):
     mdl.fit(b, opt, epochs=40, patience=1000, use_schedule=False, steps_per_epoch=parts)
