@@ -574,10 +574,11 @@ __device__ __forceinline__ void warp_partial(const Grads<NET>& g, float loss, ui
 template <int NET>
 __device__ __forceinline__ void block_publish(const float (&s_red)[kMaxSeg][kFitThreads / 32][Net<NET>::P + 2], int n_slots,
                                               uint32_t u0, uint32_t u_stride, uint32_t g_k, double* __restrict__ dst,
-                                              size_t seg_stride, size_t col_stride, size_t blk_stride, unsigned int tag = 0u) {
+                                              size_t seg_stride, size_t col_stride, size_t blk_stride, unsigned int tag = 0u,
+                                              int slot0 = 0) {
     constexpr int P = Net<NET>::P;
     constexpr int N = P + 2;
-    for (int item = threadIdx.x; item < n_slots * N; item += kFitThreads) {
+    for (int item = slot0 * N + threadIdx.x; item < n_slots * N; item += kFitThreads) {
         const int slot = item / N, q = item - slot * N;
         const uint32_t u = u0 + (uint32_t)slot * u_stride, sv = u / g_k, vb = u - sv * g_k;
         double t = 0.0;
@@ -999,15 +1000,9 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                     bar_sync(n_slots, kFitThreads);
                     warp_publish<NET>(s_red[n_slots - 1], u - G, g_k, part, (size_t)kGsumLen * kLLBlocks, kLLBlocks, tag, lane);
                 }
-                if (warp != (n_slots & 7)) bar_arrive(n_slots + 1, kFitThreads);
+                if (u + G < n_units && warp != (n_slots & 7)) bar_arrive(n_slots + 1, kFitThreads);
             }
             ORP_TRACE(1);
-            if (n_slots > 0 && warp == ((n_slots - 1) & 7)) {                  // the last unit of the step
-                bar_sync(n_slots, kFitThreads);
-                warp_publish<NET>(s_red[n_slots - 1], blockIdx.x + (uint32_t)(n_slots - 1) * G, g_k, part, (size_t)kGsumLen * kLLBlocks,
-                                  kLLBlocks, tag, lane);
-            }
-            ORP_TRACE(2);
             // the step's learning rate: Adam bias terms from a table that all threads refill together every 256 steps
             if (((barriers - 1u) & (kLrTable - 1u)) == 0u && tid < kLrTable) {
                 const double ti = s_c[ST_ADAM_T] + 1.0 + (double)tid;
@@ -1016,6 +1011,10 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
             }
             if (tid == 0) s_peer_ok = 1;
             __syncthreads();
+            // the last unit of the step is on the critical path: all threads publish it (after the step's one block barrier)
+            if (n_slots > 0)
+                block_publish<NET>(s_red, n_slots, blockIdx.x, G, g_k, part, (size_t)kGsumLen * kLLBlocks, kLLBlocks, 1, tag, n_slots - 1);
+            ORP_TRACE(2);
             if (tid == 32) {
                 double lr = s_c[ST_LR];
                 if (k == 0 && s_c[ST_USE_SCHED] != 0.0) lr = schedule_lr((int)s_c[ST_EPOCH], lr);
