@@ -232,11 +232,12 @@ int orp_fit_step(const orp_fit_batch* b, float* d_params, double* d_state, doubl
 int orp_fit_epochs(const orp_fit_batch* parts, int n_parts, float* d_params, double* d_state, double* d_gsum,
                    void* d_scratch, int n_epochs, void* stream);
 
-/* The whole epoch loop of Model.fit (Replicating_Portfolio.py:211) in ONE cooperative launch, single GPU: the batch is
- * cut into n_parts contiguous ranges of ceil(count / n_parts) samples (one optimiser step each); a grid of one thread
- * block per SM stays resident, synchronises once per step with a grid barrier, and every block applies the same
- * fixed-order reduction and Adam step to its own copy of the weights.  Runs at most n_epochs epochs and returns to
- * the host as soon as EarlyStopping fires.  Results are bit-identical to orp_fit_grad -> orp_fit_update.
+/* The whole epoch loop of Model.fit (Replicating_Portfolio.py:211) in ONE cooperative launch, single GPU: every segment
+ * of the batch is cut into n_parts contiguous ranges of ceil(count / n_parts) samples, and optimiser step k takes range k
+ * of every segment; a grid of at most one thread block per SM stays resident; there is NO grid-wide barrier: the blocks
+ * hand their totals to per-column owner blocks through tagged entries, and every block applies the same fixed-order
+ * sums and Adam step to its own copy of the weights.  Runs at most n_epochs epochs and returns to the host as soon as
+ * EarlyStopping fires.  Results are bit-identical to orp_fit_grad -> orp_fit_update (same batch, same segments).
  * d_scratch (orp_fit_scratch_bytes()) must be ZERO-FILLED once before its first use and then left alone between
  * calls: blocks hand their totals to each other through entries tagged with a step counter kept in it (no grid-wide
  * barrier).  Needs a device that supports cooperative launches (every B200 does): all blocks must be co-resident. */
@@ -245,9 +246,12 @@ int orp_fit_run(const orp_fit_batch* b, int n_parts, float* d_params, double* d_
 
 /* Multi-GPU form of orp_fit_run (one process per GPU, paths sharded by Sobol index range; no counterpart in the
  * reference, which is single-process).  The ranks' [gradient, loss, count] vectors are exchanged INSIDE the
- * persistent kernel: block 0 of every rank stores its vector into every rank's exchange buffer over NVLink, the step
- * number riding inside every 8-byte store; all blocks poll their own GPU's buffer and add the vectors in rank order,
- * so every GPU applies the same bits.  Every rank must call with the same n_parts / n_epochs and an equal local sample count.
+ * persistent kernel: the owner block of each vector column stores its column total into every rank's exchange buffer
+ * over NVLink, the step number riding inside every 8-byte element; all blocks poll their own GPU's buffer and add the
+ * ranks' totals pairwise in rank order, so every GPU applies the same bits (and, with 8 / world segments per rank, the
+ * bits of a one-GPU run).  Every rank must call with the same n_parts / n_epochs / n_seg and an equal local sample
+ * count.  All ranks must be on one host with peer access between their GPUs; a hand-over that does not complete within
+ * 60 s raises the abort flag (word ST_ABORT of the state block) instead of hanging.
  * d_peer_buffers: DEVICE array of `world` pointers, entry r = rank r's buffer as mapped into this process.
  * Exchange buffers are the one thing this library allocates itself (CUDA IPC needs a cudaMalloc'ed base):
  *   orp_peer_buffer_create  cudaMalloc + zero + IPC handle (64 bytes) to send to the other ranks

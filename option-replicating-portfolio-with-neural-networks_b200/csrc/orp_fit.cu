@@ -667,7 +667,10 @@ __device__ __forceinline__ bool unpack_raw(const FitArgs& a, const RawSample<NET
 // U x ~230 issue slots per warp: at 8 warps per SM (the 97/122 gradient accumulators take the register file)
 // there is no other warp to switch to.
 constexpr int kFitS = 2;                                   // samples per thread in flight through the network
-template <int NET> constexpr int kFitUnroll = NET == ORP_NET_EO ? 4 : 2;
+#ifndef ORP_FIT_UNROLL_EO
+#define ORP_FIT_UNROLL_EO 4
+#endif
+template <int NET> constexpr int kFitUnroll = NET == ORP_NET_EO ? ORP_FIT_UNROLL_EO : 2;
 
 // Issues the loads of this block's FIRST tile of a batch (the persistent kernel does this one optimiser step
 // ahead, so that the latency hides behind the grid barrier and the reduction).
