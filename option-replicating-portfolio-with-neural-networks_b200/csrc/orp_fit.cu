@@ -572,7 +572,7 @@ __device__ __forceinline__ void warp_partial(const Grads<NET>& g, float loss, ui
 // tag != 0: every entry is written as two 8-byte words {low half, tag}, {high half, tag} (dst counts 16-byte
 // entries), so that a reader polling for `tag` needs no barrier and no fence (8-byte accesses are single-copy atomic).
 template <int NET>
-__device__ __forceinline__ void block_publish(const float (&s_red)[kMaxSeg][kFitThreads / 32][Net<NET>::P + 2], int n_slots,
+__device__ __forceinline__ void block_publish(const float (*s_red)[kFitThreads / 32][Net<NET>::P + 2], int n_slots,
                                               uint32_t u0, uint32_t u_stride, uint32_t g_k, double* __restrict__ dst,
                                               size_t seg_stride, size_t col_stride, size_t blk_stride, unsigned int tag = 0u,
                                               int slot0 = 0) {
@@ -752,7 +752,7 @@ __global__ void __launch_bounds__(kFitThreads) fit_grad_kernel(const FitArgs a, 
     const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
 
     // one UNIT per block: block b works on virtual block b % g_k of segment b / g_k (g_k = a.g_blocks blocks per segment)
-    __shared__ float s_red[kMaxSeg][kFitThreads / 32][N::P + 2];
+    __shared__ float s_red[1][kFitThreads / 32][N::P + 2];
     const uint32_t g_k = (uint32_t)a.g_blocks, sv = blockIdx.x / g_k, vb = blockIdx.x - sv * g_k;
     {
         const FitArgs av = seg_args<T>(a, (int)sv);
@@ -913,7 +913,8 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
     __shared__ double s_g[kGsumLen];
     __shared__ double s_c[16];                     // head of the control block (ST_LR .. ST_COUNT_ACC)
     __shared__ double s_seg[kGsumLen][kMaxSeg];    // owner stage: segment totals of the columns this block owns
-    __shared__ float s_red[kMaxSeg][kFitThreads / 32][P + 2];
+    extern __shared__ __align__(16) float s_dyn[];                 // warp totals of up to kMaxSeg units: [slot][warp][P + 2]
+    float (*s_red)[kFitThreads / 32][P + 2] = reinterpret_cast<float (*)[kFitThreads / 32][P + 2]>(s_dyn);
     __shared__ float s_lr_t;
     __shared__ int s_improved;
     constexpr int kLrTable = 256;
@@ -994,16 +995,17 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
                 }
                 accumulate_tiles<NET, LOSS, T, SKIP>(a, s_wa, vb, g_k, first, g, loss, n, a_nx, vb_nx, has_nx);
                 warp_partial<NET>(g, loss, n, s_red[n_slots][warp]);
-                static_assert(kFitThreads == 256 && kMaxSeg <= 15, "eight warps take turns as publishers; barriers 1 .. kMaxSeg");
+                static_assert(kMaxSeg <= 15, "numbered barriers 1 .. kMaxSeg");
+                constexpr int NW = kFitThreads / 32;                            // the warps take turns as publishers
                 // hand-over inside the block, one unit behind: warp (slot mod 8) publishes unit `slot` once the other seven
                 // have parked its totals (numbered barrier slot + 1: they arrive without waiting, the publisher waits) —
                 // it does so after its OWN next unit, so the wait is over before it starts and the stores of all but the
                 // last unit are in L2 long before the owners look for them
-                if (n_slots > 0 && warp == ((n_slots - 1) & 7)) {
+                if (n_slots > 0 && warp == (n_slots - 1) % NW) {
                     bar_sync(n_slots, kFitThreads);
                     warp_publish<NET>(s_red[n_slots - 1], u - G, g_k, part, (size_t)kGsumLen * kLLBlocks, kLLBlocks, tag, lane);
                 }
-                if (u + G < n_units && warp != (n_slots & 7)) bar_arrive(n_slots + 1, kFitThreads);
+                if (u + G < n_units && warp != n_slots % NW) bar_arrive(n_slots + 1, kFitThreads);
             }
             ORP_TRACE(1);
             // the step's learning rate: Adam bias terms from a table that all threads refill together every 256 steps
@@ -1538,7 +1540,9 @@ static int fit_run_launch(const orp_fit_batch* b, int n_parts, float* d_params, 
     if (r.a.skip) ORP_FIT_DISPATCH(PICK_RUN_SKIP); else ORP_FIT_DISPATCH(PICK_RUN);
 #undef PICK_RUN
 #undef PICK_RUN_SKIP
-    ORP_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kFitThreads), args, 0, st));
+    const size_t dyn = (size_t)kMaxSeg * (kFitThreads / 32) * (size_t)(orp_fit_n_params(b->net) + 2) * sizeof(float);
+    ORP_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    ORP_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kFitThreads), args, dyn, st));
     return ORP_OK;
 }
 
