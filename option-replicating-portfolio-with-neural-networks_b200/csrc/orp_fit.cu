@@ -315,7 +315,7 @@ __device__ __forceinline__ void loss_grad(float y, float v, float& l, float& dv)
 struct FitArgs {
     const void* s_t; const void* s_t1; const float* feat1; const float* feat2; const float* target;
     uint64_t count;
-    float inv_scale_f; double inv_scale; float b_t, b_t1;
+    double inv_scale; float b_t, b_t1;
     int skip;                  // non-zero: samples with a non-finite input or target take no part (ORP_FIT_SKIP_NONFINITE)
     int n_seg;                 // the batch is n_seg segments of `count` samples, segment v starting seg_stride * v samples in
     int g_blocks;              // virtual blocks per segment (fit_blocks(count)): part of the sums' definition, not of the launch
@@ -1419,7 +1419,7 @@ static int make_args(const orp_fit_batch* b, FitArgs& a, bool need_target) {
     ORP_REQUIRE(!need_target || b->d_target, "null target");
     ORP_REQUIRE(b->count >= 1, "count must be >= 1");
     a.s_t = b->d_s_t; a.s_t1 = b->d_s_t1; a.feat1 = b->d_feat1; a.feat2 = b->d_feat2; a.target = b->d_target;
-    a.count = b->count; a.inv_scale = b->inv_scale; a.inv_scale_f = (float)b->inv_scale;
+    a.count = b->count; a.inv_scale = b->inv_scale;
     a.b_t = (float)(b->bond_t * b->inv_scale); a.b_t1 = (float)(b->bond_t1 * b->inv_scale);
     ORP_REQUIRE(b->paths_dtype == ORP_F64 || b->inv_scale == 1.0,
                 "fp32 price columns must be in network units already (inv_scale = 1): convert with orp_fit_scale_column");

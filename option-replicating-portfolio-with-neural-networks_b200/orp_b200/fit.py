@@ -84,6 +84,9 @@ class Optimizer:
         return self.state[self._head_idx].cpu().numpy()
 
 
+_peer_cache = {}          # (device, process group) -> mapped exchange buffers: created once per process, not per run
+
+
 class ReplicationNet:
     """The shared weights of model1/model2 plus scratch buffers; ``fit`` runs one ``Model.fit`` call."""
 
@@ -109,7 +112,13 @@ class ReplicationNet:
         if peer_exchange is None:
             peer_exchange = _nccl_group(group) and os.environ.get("ORP_B200_NO_PEERS") is None
         if peer_exchange:
-            self._setup_peers()
+            # the exchange buffers (a cudaMalloc, the IPC handle exchange and the mappings) are made once per process,
+            # device and group and shared by every model created afterwards: their step counter lives in the buffer
+            key = (str(self.device), id(group) if group is not None else None)
+            if key not in _peer_cache:
+                self._setup_peers()
+                _peer_cache[key] = self.peers
+            self.peers = _peer_cache[key]
 
     def _setup_peers(self):
         """Exchange buffers for the in-kernel all-gather of the [gradient, loss, count] vectors: every rank creates
@@ -168,19 +177,9 @@ class ReplicationNet:
         self.peers = dict(rank=rank, world=world, own=own.value, opened=opened, table=table)
 
     def close(self):
-        """Unmap the peers' buffers and free this rank's (collective: call on every rank)."""
-        if self.peers is not None:
-            L = _lib.lib()
-            torch = _lib.require_cuda()
-            with torch.cuda.device(self.device):
-                torch.cuda.synchronize()
-                if self.peers["world"] > 1:
-                    import torch.distributed as dist
-                    dist.barrier(group=self.group)    # no rank frees memory a peer's kernel may still write to
-                for q in self.peers["opened"]:
-                    L.orp_peer_buffer_close(q)
-                L.orp_peer_buffer_destroy(self.peers["own"])
-            self.peers = None
+        """Detach from the exchange buffers (they stay mapped for the next model of this process; release_peers() frees
+        them)."""
+        self.peers = None
 
     def _ranks_have_equal_counts(self, count: int) -> bool:
         if count not in self._equal_counts:
@@ -356,6 +355,25 @@ class ReplicationNet:
                 self.launches += 2
             rows = allgather_rows(self.sums, self.group)             # (world, L, 5): global segment v = rank * L + local
             return tree_sum_rows(rows.reshape(-1, 5))
+
+
+def release_peers():
+    """Unmap the peers' exchange buffers and free this rank's (collective: call on every rank, e.g. before
+    ``destroy_process_group``).  Optional: process exit releases them as well."""
+    torch = _lib.require_cuda()
+    L = _lib.lib()
+    for (dev, _), peers in list(_peer_cache.items()):
+        if peers is None:
+            continue
+        with torch.cuda.device(torch.device(dev)):
+            torch.cuda.synchronize()
+            if peers["world"] > 1:
+                import torch.distributed as dist
+                dist.barrier()                        # no rank frees memory a peer's kernel may still write to
+            for q in peers["opened"]:
+                L.orp_peer_buffer_close(q)
+            L.orp_peer_buffer_destroy(peers["own"])
+    _peer_cache.clear()
 
 
 def virtual_segments(count: int, group=None, virtual_shards: int = 8) -> int:
