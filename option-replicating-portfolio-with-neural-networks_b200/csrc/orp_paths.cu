@@ -474,11 +474,26 @@ __global__ void __launch_bounds__(128) paths_payoff_final_kernel(const double* _
 // Sobol dimension ops[o].dim and is followed by ops[o].emits emissions (pop + time step).
 struct BridgeOp { int32_t dim; int32_t emits; double wl, wr, sd; };
 constexpr int kBridgeMaxDepth = 20;
+// the schedule's bytes in shared memory (a multiple of 128 so that the stack columns behind it stay aligned)
+__host__ __device__ inline size_t bridge_ops_smem_bytes(int n_steps) { return ((size_t)n_steps * sizeof(BridgeOp) + 127) / 128 * 128; }
 
-template <int MODEL, typename OutT, bool MULT>
+// SSTK: the stack lives in shared memory behind the coefficient table and the schedule (level-major, one 8-byte
+// column per thread: conflict-free), its TOP in registers — a push stores the old top and needs no load at all, a pop
+// loads the entry below for later use.  Chosen when (depth - 1) levels fit (D <= 512 for the one-engine models);
+// otherwise the stack is a per-thread array in local memory.  With it the schedule is staged in shared memory too
+// and the lane-table entry of the next op is requested one op ahead (its Sobol dimension comes from the lanes that
+// evaluated the chunk's bases), so no step waits on two dependent global loads.
+template <int MODEL, typename OutT, bool MULT, bool SSTK>
 __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const PathArgs a, const BridgeOp* __restrict__ ops) {
     extern __shared__ __align__(128) char s_tab[];
     load_ndtri_table(reinterpret_cast<double*>(s_tab), threadIdx.x, blockDim.x);
+    const int D = a.n_steps;
+    BridgeOp* s_ops = reinterpret_cast<BridgeOp*>(s_tab + kNdtriTableBytes);
+    if (SSTK) {
+        const ulonglong2* src = reinterpret_cast<const ulonglong2*>(ops);
+        ulonglong2* dst = reinterpret_cast<ulonglong2*>(s_ops);
+        for (int i = threadIdx.x; i < D * 2; i += blockDim.x) dst[i] = src[i];
+    }
     __syncthreads();
 
     const uint32_t tab = (uint32_t)__cvta_generic_to_shared(s_tab);
@@ -488,7 +503,9 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
     const uint64_t end = a.start + a.count;
     const uint64_t w_first = a.start / kWarpPaths, w_last = (end - 1) / kWarpPaths;
     const uint64_t n_tiles = w_last - w_first + 1;
-    const int D = a.n_steps;
+    const BridgeOp* __restrict__ prog = SSTK ? s_ops : ops;
+    // level l of stack q of this thread: s_stk[(l * NS + q) * kPathThreads]
+    double* s_stk = reinterpret_cast<double*>(s_tab + kNdtriTableBytes + bridge_ops_smem_bytes(D)) + threadIdx.x;
 
     for (uint64_t tile = (uint64_t)blockIdx.x * kWarps + warp; tile < n_tiles; tile += (uint64_t)gridDim.x * kWarps) {
         const uint64_t w = w_first + tile;
@@ -501,46 +518,76 @@ __global__ void __launch_bounds__(kPathThreads, 1) paths_bridge_kernel(const Pat
         if (ok0) store_col<OutT>(a.out, a.ld, 0, j0, a.s0);
         if (ok1) store_col<OutT>(a.out, a.ld, 0, j1, a.s0);
         int next_keep = a.keep_every, col = 1, t = 0, sp = -1;
-        double stk[NS][kBridgeMaxDepth];
+        double stk[NS][SSTK ? 1 : kBridgeMaxDepth];
+        double top[NS];                                      // SSTK: the stack's top entry (valid while sp >= 0)
         double cur[NS];
 #pragma unroll
-        for (int q = 0; q < NS; ++q) cur[q] = 0.0;           // W(0) = 0
+        for (int q = 0; q < NS; ++q) { cur[q] = 0.0; top[q] = 0.0; }           // W(0) = 0
 
         for (int o0 = 0; o0 < D; o0 += 32) {
             uint32_t bl_a = 0u, bl_b = 0u;
+            int my_dim = 0;
             if (o0 + lane < D) {
-                const int my_dim = ops[o0 + lane].dim;
+                my_dim = prog[o0 + lane].dim;
                 bl_a = warp_base(a.sv32_a, a.dpad, my_dim, w);
                 if (MODEL == ORP_MODEL_SV) bl_b = warp_base(a.sv32_b, a.dpad, my_dim, w);
             }
             const int nc = min(32, D - o0);
+            uint2 tl_next = make_uint2(0u, 0u), tb_next = make_uint2(0u, 0u);
+            if (SSTK) {
+                const int d0 = __shfl_sync(kFull, my_dim, 0);
+                tl_next = __ldg(a.tlane_a + (size_t)d0 * 32 + lane);
+                if (MODEL == ORP_MODEL_SV) tb_next = __ldg(a.tlane_b + (size_t)d0 * 32 + lane);
+            }
             for (int s = 0; s < nc; ++s) {
-                const BridgeOp op = ops[o0 + s];
+                const BridgeOp op = prog[o0 + s];
                 double zz[NS];
+                uint2 tl, tb = make_uint2(0u, 0u);
+                if (SSTK) {
+                    tl = tl_next; tb = tb_next;
+                    const int dn = __shfl_sync(kFull, my_dim, (s + 1) & 31);       // past the chunk: a valid row, value unused
+                    tl_next = __ldg(a.tlane_a + (size_t)dn * 32 + lane);
+                    if (MODEL == ORP_MODEL_SV) tb_next = __ldg(a.tlane_b + (size_t)dn * 32 + lane);
+                } else {
+                    tl = __ldg(a.tlane_a + (size_t)op.dim * 32 + lane);
+                    if (MODEL == ORP_MODEL_SV) tb = __ldg(a.tlane_b + (size_t)op.dim * 32 + lane);
+                }
                 {
                     const uint32_t base = __shfl_sync(kFull, bl_a, s);
-                    const uint2 tl = __ldg(a.tlane_a + (size_t)op.dim * 32 + lane);
                     zz[0] = ndtri_bits(base ^ tl.x, tab);
                     zz[1] = ndtri_bits(base ^ tl.y, tab);
                 }
                 if (MODEL == ORP_MODEL_SV) {
                     const uint32_t base_b = __shfl_sync(kFull, bl_b, s);
-                    const uint2 tb = __ldg(a.tlane_b + (size_t)op.dim * 32 + lane);
                     zz[NS - 2] = ndtri_bits(base_b ^ tb.x, tab);
                     zz[NS - 1] = ndtri_bits(base_b ^ tb.y, tab);
                 }
                 // W_m = wl W_left + wr W_right + sd z   (left = last emitted node, right = stack top)
 #pragma unroll
                 for (int q = 0; q < NS; ++q) {
-                    const double right = sp >= 0 ? stk[q][sp] : 0.0;
-                    stk[q][sp + 1] = op.wl * cur[q] + op.wr * right + op.sd * zz[q];
+                    if (SSTK) {
+                        const double right = sp >= 0 ? top[q] : 0.0;
+                        if (sp >= 0) s_stk[(size_t)(sp * NS + q) * kPathThreads] = top[q];
+                        top[q] = op.wl * cur[q] + op.wr * right + op.sd * zz[q];
+                    } else {
+                        const double right = sp >= 0 ? stk[q][sp] : 0.0;
+                        stk[q][sp + 1] = op.wl * cur[q] + op.wr * right + op.sd * zz[q];
+                    }
                 }
                 ++sp;
                 for (int e = 0; e < op.emits; ++e) {
                     double inc[NS];
 #pragma unroll
-                    for (int q = 0; q < NS; ++q) { const double wj = stk[q][sp]; inc[q] = wj - cur[q]; cur[q] = wj; }
+                    for (int q = 0; q < NS; ++q) {
+                        const double wj = SSTK ? top[q] : stk[q][sp];
+                        inc[q] = wj - cur[q];
+                        cur[q] = wj;
+                    }
                     --sp;
+                    if (SSTK && sp >= 0) {
+#pragma unroll
+                        for (int q = 0; q < NS; ++q) top[q] = s_stk[(size_t)(sp * NS + q) * kPathThreads];
+                    }
                     ++t;
                     advance<MODEL, MULT>(a, s_0, s_1, v_0, v_1, inc[0], inc[1], inc[NS - 2], inc[NS - 1]);
                     if (t == next_keep) {
@@ -602,25 +649,47 @@ static int launch_paths(const PathArgs& a, cudaStream_t st) {
 }
 
 
-template <int MODEL, typename OutT, bool MULT>
-static int launch_paths_bridge_v(const PathArgs& a, const void* d_bridge, cudaStream_t st) {
-    int rc = set_table_smem(paths_bridge_kernel<MODEL, OutT, MULT>);
+// Deepest stack of the depth-first bridge walk over D steps (the walk of orp_bridge_schedule without the weights).
+static int bridge_depth(int D) {
+    std::vector<int> stack{D};
+    int left = 0, depth = 1;
+    for (int j = 1; j <= D; ++j) {
+        while (stack.back() > j) {
+            stack.push_back((left + stack.back()) / 2);
+            if ((int)stack.size() > depth) depth = (int)stack.size();
+        }
+        stack.pop_back();
+        left = j;
+    }
+    return depth;
+}
+
+template <int MODEL, typename OutT, bool MULT, bool SSTK>
+static int launch_paths_bridge_v(const PathArgs& a, const void* d_bridge, size_t smem, cudaStream_t st) {
+    int rc = set_table_smem(paths_bridge_kernel<MODEL, OutT, MULT, SSTK>, smem);
     if (rc) return rc;
     const uint64_t n_tiles = (a.start + a.count - 1) / kWarpPaths - a.start / kWarpPaths + 1;
     const uint64_t want = (n_tiles + 31) / 32;
     const int grid = (int)(want < (uint64_t)sm_count() ? want : (uint64_t)sm_count());
-    paths_bridge_kernel<MODEL, OutT, MULT><<<grid, kPathThreads, kNdtriTableBytes, st>>>(a, reinterpret_cast<const BridgeOp*>(d_bridge));
+    paths_bridge_kernel<MODEL, OutT, MULT, SSTK><<<grid, kPathThreads, smem, st>>>(a, reinterpret_cast<const BridgeOp*>(d_bridge));
     ORP_LAUNCH_CHECK("paths_bridge_kernel");
     return ORP_OK;
 }
 
 template <int MODEL, typename OutT>
 static int launch_paths_bridge(const PathArgs& a, const void* d_bridge, cudaStream_t st) {
+    constexpr size_t n_stacks = MODEL == ORP_MODEL_SV ? 4 : 2;
+    // the top entry stays in registers: depth - 1 levels of one 8-byte column per thread and stack
+    const size_t with_stack = kNdtriTableBytes + bridge_ops_smem_bytes(a.n_steps)
+                              + (size_t)(bridge_depth(a.n_steps) - 1) * n_stacks * kPathThreads * sizeof(double);
+    const bool sstk = with_stack <= kMaxDynSmem && !getenv("ORP_B200_NO_SMEM_STACK");
     if constexpr (MODEL == ORP_MODEL_GBM_LOG || MODEL == ORP_MODEL_SV) {
         if (a.keep_every <= 2 && small_steps(a, MODEL) && !getenv("ORP_B200_NO_MULT"))
-            return launch_paths_bridge_v<MODEL, OutT, true>(a, d_bridge, st);
+            return sstk ? launch_paths_bridge_v<MODEL, OutT, true, true>(a, d_bridge, with_stack, st)
+                        : launch_paths_bridge_v<MODEL, OutT, true, false>(a, d_bridge, kNdtriTableBytes, st);
     }
-    return launch_paths_bridge_v<MODEL, OutT, false>(a, d_bridge, st);
+    return sstk ? launch_paths_bridge_v<MODEL, OutT, false, true>(a, d_bridge, with_stack, st)
+                : launch_paths_bridge_v<MODEL, OutT, false, false>(a, d_bridge, kNdtriTableBytes, st);
 }
 
 // PathArgs of a launch from the caller's parameter block (shared by orp_paths and orp_paths_payoff)
