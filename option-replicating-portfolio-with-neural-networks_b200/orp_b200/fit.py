@@ -514,6 +514,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
         phi0, psi0, v0 = rec["phi"], rec["psi"], rec["mean_V"]
         first = False
     out = {"V0": v0, "phi0": phi0, "psi0": psi0, "steps": steps, "launches": model.launches,
-           "params": model.params[:model.P].cpu().numpy(), "values0": v_next}
+           "params": model.params[:model.P].cpu().numpy(), "values0": v_next,
+           "virtual_shards": int(virtual_shards) if mode == "scaled" else 1}
     model.close()
     return out

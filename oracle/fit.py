@@ -191,7 +191,7 @@ def backward_replication(S_cols: np.ndarray, B_cols: np.ndarray, terminal_value:
                          out_bias=None, batch_size=512, shuffle_seed: int = 0,
                          epochs_first: int = 500, epochs_next: int = 100,
                          patience_first: int = 50, patience_next: int = 7,
-                         features=None, cuda_perm: bool = False):
+                         features=None, cuda_perm: bool = False, batch_order=None):
     """The loop ``for t_i in range(n-2, -1, -1)`` of ``European Options.ipynb`` cell 13 (model1
     only, ``values[:, t_i] = g_t``); with ``net='rp'`` the MSE half of
     ``Replicating_Portfolio.py:193-221``.
@@ -199,6 +199,9 @@ def backward_replication(S_cols: np.ndarray, B_cols: np.ndarray, terminal_value:
     ``S_cols``: (paths, n) kept columns; ``B_cols``: (n,); ``terminal_value``: (paths,) already in
     network units (EO: ``payoff / S0``).  ``scale`` divides prices (EO: ``ADJUSTMENT_FACTOR = S0``).
     ``features(t_i)`` supplies the extra RP inputs ``(N_t/N, lambda_t)``; default 1 and 0.
+    ``batch_order`` (optional, position -> sample index, the same every epoch): the make-up of the optimiser steps
+    when it is not "consecutive index ranges" — the CUDA path's virtual shards take step ``k`` from the ``k``-th range
+    of every shard (``orp_b200.fit.ReplicationNet.split``).
     Returns ``dict(V0, phi0, psi0, values, history)`` in network units (times ``scale`` for EO's
     ``V0_RP``)."""
     n_paths, n = S_cols.shape
@@ -227,7 +230,8 @@ def backward_replication(S_cols: np.ndarray, B_cols: np.ndarray, terminal_value:
         h = fit(params, opt, net, x, p1, y, epochs=epochs_first if first else epochs_next,
                 patience=patience_first if first else patience_next, use_schedule=first,
                 batch_size=batch_size, shuffle_rng=rng,
-                perm_fn=(lambda e, t_i=t_i: minibatch_perm(n_paths, (shuffle_seed * 4096 + 2 * t_i) * 1_000_003 + e))
+                perm_fn=(lambda e: np.asarray(batch_order, dtype=np.int64)) if batch_order is not None else
+                (lambda e, t_i=t_i: minibatch_perm(n_paths, (shuffle_seed * 4096 + 2 * t_i) * 1_000_003 + e))
                 if (cuda_perm and batch_size is not None) else None)
         with torch.no_grad():
             g_t, phi, psi = forward(params, net, x, p0)
