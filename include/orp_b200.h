@@ -312,6 +312,30 @@ int orp_select_hist(const float* d_x, uint64_t n, int shift, uint32_t prefix, ui
                     unsigned long long* d_hist, void* stream);
 int orp_select_next(const float* d_x, uint64_t n, uint32_t key, unsigned long long* d_out, void* stream);
 
+/* The same selection with the digit picked ON THE DEVICE, for n_q <= ORP_SELECT_MAX_Q order statistics at once (the two
+ * quantiles of Replicating_Portfolio.py:122 share every pass over the array; no host round trip between passes).
+ * d_state[q]: the caller sets k = rank of the wanted element (0-based, over all ranks' elements) and zeroes the rest.
+ *   for shift in 24, 16, 8, 0:
+ *     orp_select_hist_multi  ADDS the n_q histograms (d_hist[n_q][ORP_SELECT_BINS], zero before the first pass);
+ *     [several GPUs: sum d_hist over the ranks];
+ *     orp_select_pick        descends into the digit that holds rank k (updates k, prefix, mask), sets `nan` when the
+ *                            array holds a NaN and `bad` when k is beyond the element count, and zeroes d_hist again;
+ *   orp_select_next_multi    d_out[q][0] += #{key <= prefix_q}, d_out[q][1] = min(., smallest key above prefix_q)
+ *                            (caller initialises d_out[q] = {0, 0xffffffff}; several GPUs: sum / min over the ranks).
+ * Afterwards d_state[q].prefix is the order-preserving key of the k-th smallest element. */
+#define ORP_SELECT_MAX_Q 4
+typedef struct orp_select_state {
+    unsigned long long k;      /* in: rank wanted; during the passes: rank inside the digits chosen so far */
+    uint32_t prefix, mask;     /* digits chosen so far and the bits they cover */
+    uint32_t nan, bad;         /* out: a NaN was seen / k was beyond the number of elements */
+    unsigned long long reserved;
+} orp_select_state;
+int orp_select_hist_multi(const float* d_x, uint64_t n, int shift, int n_q, const orp_select_state* d_state,
+                          unsigned long long* d_hist, void* stream);
+int orp_select_pick(unsigned long long* d_hist, int shift, int n_q, orp_select_state* d_state, void* stream);
+int orp_select_next_multi(const float* d_x, uint64_t n, int n_q, const orp_select_state* d_state,
+                          unsigned long long* d_out, void* stream);
+
 /* ---------------------------------------------------------------- §8f-2  survivors (device) */
 
 /* Replaces the binomial thinning loop of Replicating_Portfolio.py:78-84 for path counts the host loop cannot reach:

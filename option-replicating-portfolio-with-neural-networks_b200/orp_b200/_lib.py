@@ -91,6 +91,9 @@ PROTOTYPES = {
     "orp_fit_residuals": (C.c_int, [C.POINTER(FitBatch), _vp, _vp, _vp]),
     "orp_select_hist": (C.c_int, [_vp, _u64, _i32, C.c_uint32, C.c_uint32, _vp, _vp]),
     "orp_select_next": (C.c_int, [_vp, _u64, C.c_uint32, _vp, _vp]),
+    "orp_select_hist_multi": (C.c_int, [_vp, _u64, _i32, _i32, _vp, _vp, _vp]),
+    "orp_select_pick": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
+    "orp_select_next_multi": (C.c_int, [_vp, _u64, _i32, _vp, _vp, _vp]),
     "orp_survivors": (C.c_int, [_vp, _i32, _u64, _u64, _u64, _i32, _i32, _f64, _f64, _u64, _vp, _u64, _vp]),
     "orp_fit_epoch_minibatch": (C.c_int, [C.POINTER(FitBatch), _vp, _vp, _i32, _u64, _vp]),
     "orp_probe_throughput": (C.c_int, [_i32, _i32, _vp, C.POINTER(C.c_double), _vp]),

@@ -503,7 +503,7 @@ def fit_replication(paths_tm, bond, terminal_values, *, net: str = "eo", mode: s
             if resid_buf is None:
                 resid_buf = torch.empty_like(v_next)
             model.residuals(b2 if second_model else b, resid_buf)          # weights as they stand after the step's fits
-            rec["VaR"] = quantiles(resid_buf, var_quantiles, group, ignore_nan=skip_nonfinite).tolist()
+            rec["VaR"] = quantiles(resid_buf, var_quantiles, group, ignore_nan=skip_nonfinite, total=int(total)).tolist()
         steps.append(rec)
         if on_step_end is not None:
             on_step_end(rec)

@@ -3,8 +3,9 @@ reference prints as ``VaR: ... (98%), ... (99%)`` at every time step (``Replicat
 ``np.quantile`` over one value per path).  The reference appends every residual to a Python list, which cannot
 scale; here the array never leaves the GPU: a radix select over its order-preserving integer keys (four 8-bit
 passes pin the k-th smallest element exactly, one more finds its successor for NumPy's linear interpolation).
-With ``torch.distributed`` initialised the ranks' histograms are summed between passes, so every rank returns the
-quantile of the WHOLE path set.
+All requested quantiles share the five passes, the digit is picked on the device between passes
+(``orp_select_pick``) and the host reads the result once.  With ``torch.distributed`` initialised the ranks'
+histograms are summed between passes, so every rank returns the quantile of the WHOLE path set.
 """
 from __future__ import annotations
 
@@ -21,79 +22,88 @@ def _key_to_float(key: int) -> float:
     return float(np.array([bits], dtype=np.uint32).view(np.float32)[0])
 
 
-def _kth_key(x, k: int, group, ignore_nan: bool = False):
-    """Order-preserving key of the k-th smallest element (0-based) over all ranks; None when a NaN is present
-    (unless NaNs are ignored: they are never histogrammed, so they simply do not take part)."""
+MAX_Q = 4                      # ORP_SELECT_MAX_Q: order statistics per set of passes
+
+
+def _select(x, ks, group):
+    """Order-preserving keys of the ``ks``-th smallest elements (0-based ranks over all ranks' elements; at most
+    ``MAX_Q``), with the count of elements <= each key and the smallest key above it: ``(keys, le, nxt, nan, bad)``.
+    Nothing is read back before the last pass: the selection state lives in device memory."""
     torch = _lib.require_cuda()
+    import torch.distributed as dist
     L = _lib.lib()
-    hist = torch.zeros(BINS, dtype=torch.int64, device=x.device)
-    prefix = mask = 0
+    Q = len(ks)
+    st_host = np.zeros((Q, 4), dtype=np.uint64)            # orp_select_state: k | prefix, mask | nan, bad | reserved
+    st_host[:, 0] = ks
+    state = torch.from_numpy(st_host.view(np.int64)).to(x.device)
+    hist = torch.zeros(Q * BINS, dtype=torch.int64, device=x.device)
+    out = torch.tensor([0, 0xFFFFFFFF] * Q, dtype=torch.int64, device=x.device)
+    sp = _lib.stream_ptr()
     for shift in (24, 16, 8, 0):
-        hist.zero_()
-        _lib.check(L.orp_select_hist(_lib.ptr(x), x.numel(), shift, prefix, mask, _lib.ptr(hist), _lib.stream_ptr()))
+        _lib.check(L.orp_select_hist_multi(_lib.ptr(x), x.numel(), shift, Q, _lib.ptr(state), _lib.ptr(hist), sp))
         allreduce_sum_(hist, group)
-        h = hist.cpu().numpy()
-        if h[256] > 0 and not ignore_nan:
-            return None
-        cum = np.cumsum(h[:256])
-        d = int(np.searchsorted(cum, k, side="right"))
-        if d > 255:
-            raise ValueError("rank k is beyond the number of elements")
-        k -= int(cum[d - 1]) if d else 0
-        prefix |= d << shift
-        mask |= 0xFF << shift
-    return prefix
-
-
-def _successor(x, key: int, group):
-    """(#elements <= key, smallest key above it) over all ranks."""
-    torch = _lib.require_cuda()
-    out = torch.tensor([0, 0xFFFFFFFF], dtype=torch.int64, device=x.device)
-    _lib.check(_lib.lib().orp_select_next(_lib.ptr(x), x.numel(), key, _lib.ptr(out), _lib.stream_ptr()))
+        _lib.check(L.orp_select_pick(_lib.ptr(hist), shift, Q, _lib.ptr(state), sp))
+    _lib.check(L.orp_select_next_multi(_lib.ptr(x), x.numel(), Q, _lib.ptr(state), _lib.ptr(out), sp))
+    o = out.view(Q, 2)
     if is_distributed(group):
-        import torch.distributed as dist
-        cnt, mn = out[:1].clone(), out[1:].clone()
+        cnt, mn = o[:, 0].contiguous(), o[:, 1].contiguous()
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(mn, op=dist.ReduceOp.MIN, group=group)
-        return int(cnt), int(mn)
-    o = out.cpu().numpy()
-    return int(o[0]), int(o[1])
+        o = torch.stack([cnt, mn], dim=1)
+    both = torch.cat([state.view(-1), o.reshape(-1)]).cpu().numpy()              # the one read-back
+    st = both[:4 * Q].view(np.uint64).reshape(Q, 4)
+    o = both[4 * Q:].reshape(Q, 2)
+    keys = (st[:, 1] & np.uint64(0xFFFFFFFF)).astype(np.int64)
+    nan = ((st[:, 2] & np.uint64(0xFFFFFFFF)) != 0)
+    bad = ((st[:, 2] >> np.uint64(32)) != 0)
+    return keys, o[:, 0], o[:, 1], nan, bad
 
 
-def quantiles(x, qs, group=None, ignore_nan: bool = False) -> np.ndarray:
+def quantiles(x, qs, group=None, ignore_nan: bool = False, total: int | None = None) -> np.ndarray:
     """``np.quantile(x, qs)`` (linear interpolation) of a contiguous CUDA fp32 vector ``x`` — of the concatenation
     of every rank's ``x`` when distributed.  Returns float64; NaN if any element is NaN, like NumPy — or, with
-    ``ignore_nan=True``, ``np.nanquantile``."""
+    ``ignore_nan=True``, ``np.nanquantile``.  ``total``: the number of elements over all ranks when the caller knows
+    it (saves the one collective + read-back that counts them)."""
     torch = _lib.require_cuda()
     if x.dtype != torch.float32 or not x.is_contiguous() or x.dim() != 1:
         raise ValueError("x must be a contiguous 1-D float32 CUDA tensor")
     qs = np.atleast_1d(np.asarray(qs, dtype=np.float64))
     if ((qs < 0) | (qs > 1)).any():
         raise ValueError("Quantiles must be in the range [0, 1]")          # numpy's message
-    n = torch.tensor([x.numel()], dtype=torch.int64, device=x.device)
-    if ignore_nan:
-        n -= torch.isnan(x).sum()
-    allreduce_sum_(n, group)
-    n = int(n)
+    if total is not None and not ignore_nan:
+        n = int(total)
+    elif not ignore_nan and not is_distributed(group):
+        n = x.numel()
+    else:
+        n = torch.tensor([x.numel()], dtype=torch.int64, device=x.device)
+        if ignore_nan:
+            n -= torch.isnan(x).sum()
+        allreduce_sum_(n, group)
+        n = int(n)
     if n == 0:
         return np.full(qs.shape, np.nan)
     out = np.empty(qs.shape)
+    flat = out.reshape(-1)
+    qf = qs.reshape(-1)
     with torch.cuda.device(x.device):
-        for j, q in enumerate(qs):
-            h = (n - 1) * q
-            k = int(np.floor(h))
+        for j0 in range(0, qf.size, MAX_Q):
+            h = (n - 1) * qf[j0:j0 + MAX_Q]
+            k = np.floor(h).astype(np.int64)
             g = h - k
-            key = _kth_key(x, k, group, ignore_nan)
-            if key is None:
-                out[:] = np.nan
+            keys, le, nxt, nan, bad = _select(x, k, group)
+            if nan.any() and not ignore_nan:           # (first: NaNs are not histogrammed, so they also leave k "beyond")
+                out[...] = np.nan
                 break
-            a = _key_to_float(key)
-            b = a
-            if k + 1 < n:                            # NumPy forms (b - a) * g even when g == 0 (matters only for infinities)
-                le, nxt = _successor(x, key, group)
-                if le <= k + 1:                      # no duplicate of a at rank k + 1: the successor is the next distinct value
-                    b = _key_to_float(nxt)
-            out[j] = a + (b - a) * g if g < 0.5 else b - (b - a) * (1.0 - g)     # numpy's _lerp
+            if bad.any():
+                raise ValueError("rank k is beyond the number of elements")
+            for j in range(k.size):
+                a = _key_to_float(int(keys[j]))
+                b = a
+                # NumPy forms (b - a) * g even when g == 0 (matters only for infinities); no duplicate of a at rank
+                # k + 1 means the successor is the next distinct value
+                if k[j] + 1 < n and le[j] <= k[j] + 1:
+                    b = _key_to_float(int(nxt[j]))
+                flat[j0 + j] = a + (b - a) * g[j] if g[j] < 0.5 else b - (b - a) * (1.0 - g[j])     # numpy's _lerp
     return out
 
 

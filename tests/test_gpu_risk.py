@@ -140,3 +140,37 @@ def test_device_survivors_one_step_binomial_moments(cuda):
         mean, var = float(deaths.mean()), float(deaths.var())
         assert abs(mean - N * q) < 5 * np.sqrt(N * q * (1 - q) / n_paths) + 1e-3 * N * q, (mean, N * q)
         assert abs(var / (N * q * (1 - q)) - 1) < 0.03, (var, N * q * (1 - q))
+
+
+def test_host_picked_and_device_picked_selection_agree(cuda):
+    """The two forms of the C ABI: orp_select_hist / orp_select_next with the digit picked by the caller between
+    passes, and orp_select_hist_multi / orp_select_pick / orp_select_next_multi with the state on the device."""
+    from orp_b200 import _lib
+    from orp_b200.risk import _select, BINS
+    L = _lib.lib()
+    rng = np.random.default_rng(3)
+    x = torch.from_numpy(np.round(rng.standard_normal(200_001) * 50).astype(np.float32) / 8).to(cuda)     # many ties
+    ks = np.array([0, 1234, 100_000, 200_000])
+    keys, le, nxt, nan, bad = _select(x, ks, None)
+    assert not nan.any() and not bad.any()
+    srt = np.sort(x.cpu().numpy())
+    for j, k in enumerate(ks):
+        hist = torch.zeros(BINS, dtype=torch.int64, device=cuda)
+        prefix = mask = 0
+        kk = int(k)
+        for shift in (24, 16, 8, 0):
+            hist.zero_()
+            _lib.check(L.orp_select_hist(_lib.ptr(x), x.numel(), shift, prefix, mask, _lib.ptr(hist), _lib.stream_ptr()))
+            cum = np.cumsum(hist.cpu().numpy()[:256])
+            d = int(np.searchsorted(cum, kk, side="right"))
+            kk -= int(cum[d - 1]) if d else 0
+            prefix |= d << shift
+            mask |= 0xFF << shift
+        out = torch.tensor([0, 0xFFFFFFFF], dtype=torch.int64, device=cuda)
+        _lib.check(L.orp_select_next(_lib.ptr(x), x.numel(), prefix, _lib.ptr(out), _lib.stream_ptr()))
+        o = out.cpu().numpy()
+        assert (prefix, int(o[0]), int(o[1])) == (int(keys[j]), int(le[j]), int(nxt[j]))
+        from orp_b200.risk import _key_to_float
+        assert _key_to_float(prefix) == srt[k] and int(o[0]) == int((srt <= srt[k]).sum())
+    # k beyond the element count is reported, not silently clamped
+    assert _select(x, np.array([x.numel()]), None)[4].all()
