@@ -149,7 +149,7 @@ def test_host_picked_and_device_picked_selection_agree(cuda):
     from orp_b200.risk import _select, BINS
     L = _lib.lib()
     rng = np.random.default_rng(3)
-    x = torch.from_numpy(np.round(rng.standard_normal(200_001) * 50).astype(np.float32) / 8).to(cuda)     # many ties
+    x = torch.from_numpy(np.round(rng.standard_normal(200_001) * 50).astype(np.float32) / 8 + 0.0625).to(cuda)     # many ties, no +-0
     ks = np.array([0, 1234, 100_000, 200_000])
     keys, le, nxt, nan, bad = _select(x, ks, None)
     assert not nan.any() and not bad.any()
