@@ -103,7 +103,7 @@ template <int MODEL> constexpr bool kLevel = MODEL == ORP_MODEL_GBM_ARITH || MOD
 // |x| < 1/8 (remainder x^10 / 10! < 3e-16 relative), the library exp outside — including -inf, +inf and NaN,
 // which fail the comparison.  The host only selects MULT when six standard deviations stay inside the fast range.
 // (coefficients in constant memory: as literals each use costs two moves into uniform registers, and the stochastic-volatility
-//  loop — 370 instructions per step of which 106 are fp64 arithmetic — is bound by issue slots, not by the fp64 pipe)
+//  loop — 234 executed instructions per step of two paths, issue slots 75 % busy under ncu — is bound by issue, not by the fp64 pipe)
 __constant__ double c_exp_series[8] = {1.0 / 362880.0, 1.0 / 40320.0, 1.0 / 5040.0, 1.0 / 720.0, 1.0 / 120.0, 1.0 / 24.0, 1.0 / 6.0, 0.5};
 __device__ __forceinline__ double exp_series(double x) {
     double p = c_exp_series[0];
