@@ -1204,8 +1204,10 @@ __global__ void __launch_bounds__(kFitThreads) fit_run_kernel(const RunArgs r, f
 
 // a-10 / a-11: roll-back values at prices@t and the hedge-weight sums.
 constexpr int kPredictSums = 5;      // sum V, sum phi, sum psi, sum |y - V1|, sum |y - V1| / max(|y|, 1e-7)
+constexpr int kPredS = 2;            // samples per thread and iteration (packed arithmetic: one FFMA2 serves both)
+constexpr int kPredBlocksPerSM = 3;
 template <int NET, typename T>
-__global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitArgs a, const float* __restrict__ params,
+__global__ void __launch_bounds__(kFitThreads, kPredBlocksPerSM) fit_predict_kernel(const FitArgs a, const float* __restrict__ params,
                                                                   float* __restrict__ values_out, double* __restrict__ partials) {
     using N = Net<NET>;
     __shared__ __align__(16) float s_w[kSmemW];
@@ -1213,38 +1215,56 @@ __global__ void __launch_bounds__(kFitThreads, 4) fit_predict_kernel(const FitAr
     __syncthreads();
     const uint32_t s_wa = (uint32_t)__cvta_generic_to_shared(s_w);
     double sv = 0.0, sphi = 0.0, spsi = 0.0, sae = 0.0, sape = 0.0;
-    // One sample per thread and iteration (memory-bound: occupancy at 64 registers beats weight reuse here); the
-    // loads of the thread's NEXT sample are issued before the arithmetic of the current one, which doubles the bytes
-    // in flight per SM (32 warps x 20 B x 32 lanes alone do not cover the HBM latency-bandwidth product).
-    const uint64_t stride = (uint64_t)gridDim.x * kFitThreads;
-    uint64_t i = (uint64_t)blockIdx.x * kFitThreads + threadIdx.x;
-    RawSample<NET, T> nxt;
-    nxt.s_t = nxt.s_t1 = T(0); nxt.y = nxt.f1 = nxt.f2 = 0.f;
-    if (i < a.count) load_raw_any<NET, T>(a, i, nxt);
-    for (; i < a.count; i += stride) {
-        const RawSample<NET, T> cur = nxt;
-        if (i + stride < a.count) load_raw_any<NET, T>(a, i + stride, nxt);
-        float x[1][N::IN], s_t[1], s_t1[1], phi[1], psi[1], v0[1], tgt;
-        Acts<NET, 1> act;
-        unpack_raw<NET, T, false>(a, cur, x[0], s_t1[0], tgt);
-        s_t[0] = x[0][0];
-        net_forward<NET, 1>(s_wa, x, s_t, a.b_t, act, phi, psi, v0);          // model.predict(X0): prices at t
-        const float v1 = fmaf(phi[0], s_t1[0], psi[0] * a.b_t1);              // model.predict(X1): prices at t+1
-        if (a.skip) {                                      // opt-in: a path with a non-finite feature, price or target
-            bool fin = isfinite(s_t1[0]) && isfinite(tgt); // stays marked (NaN) and out of the sums
+    // A block walks chunks of kPredS x 256 consecutive samples; a thread owns samples t and t + 256 of the chunk (full-line
+    // warp accesses) and pushes both through the network together.  The loads of the thread's NEXT pair are issued before
+    // the arithmetic of the current one: with three blocks per SM that is 768 x 2 x 2 samples (37 KB of fp32 columns) in
+    // flight per SM, above the HBM latency-bandwidth product per SM (~35 KB); one sample per thread at four blocks per
+    // SM (25 KB) left the pass latency-bound (long_scoreboard 72 % of the stall samples, 3.3 TB/s).
+    constexpr uint64_t chunk = (uint64_t)kPredS * kFitThreads;
+    const uint64_t stride = (uint64_t)gridDim.x * chunk;
+    uint64_t i0 = (uint64_t)blockIdx.x * chunk + threadIdx.x;
+    RawSample<NET, T> nxt[kPredS];
 #pragma unroll
-            for (int q = 0; q < N::IN; ++q) fin = fin && isfinite(x[0][q]);
-            if (!fin) {
-                if (values_out) values_out[i] = __int_as_float(0x7fc00000);
-                continue;
-            }
+    for (int s = 0; s < kPredS; ++s) {
+        nxt[s].s_t = nxt[s].s_t1 = T(0); nxt[s].y = nxt[s].f1 = nxt[s].f2 = 0.f;
+        if (i0 + s * kFitThreads < a.count) load_raw_any<NET, T>(a, i0 + s * kFitThreads, nxt[s]);
+    }
+    for (; i0 < a.count; i0 += stride) {
+        RawSample<NET, T> cur[kPredS];
+#pragma unroll
+        for (int s = 0; s < kPredS; ++s) {
+            cur[s] = nxt[s];
+            if (i0 + stride + s * kFitThreads < a.count) load_raw_any<NET, T>(a, i0 + stride + s * kFitThreads, nxt[s]);
         }
-        if (values_out) values_out[i] = v0[0];
-        sv += v0[0]; sphi += phi[0]; spsi += psi[0];
-        if (a.target) {                                                       // metrics of model.evaluate(X1, ...), RP.py:215
-            const float ae = fabsf(tgt - v1);
-            sae += ae;                                                        // 'mae'
-            sape += ae / fmaxf(fabsf(tgt), 1e-7f);                            // 'mape' (Keras: |y - v| / max(|y|, epsilon), x 100 on the host)
+        float x[kPredS][N::IN], s_t[kPredS], s_t1[kPredS], phi[kPredS], psi[kPredS], v0[kPredS], tgt[kPredS];
+        Acts<NET, kPredS> act;
+#pragma unroll
+        for (int s = 0; s < kPredS; ++s) {
+            unpack_raw<NET, T, false>(a, cur[s], x[s], s_t1[s], tgt[s]);
+            s_t[s] = x[s][0];
+        }
+        net_forward<NET, kPredS>(s_wa, x, s_t, a.b_t, act, phi, psi, v0);     // model.predict(X0): prices at t
+#pragma unroll
+        for (int s = 0; s < kPredS; ++s) {
+            const uint64_t i = i0 + s * kFitThreads;
+            if (i >= a.count) continue;
+            const float v1 = fmaf(phi[s], s_t1[s], psi[s] * a.b_t1);          // model.predict(X1): prices at t+1
+            if (a.skip) {                                      // opt-in: a path with a non-finite feature, price or target
+                bool fin = isfinite(s_t1[s]) && isfinite(tgt[s]);             // stays marked (NaN) and out of the sums
+#pragma unroll
+                for (int q = 0; q < N::IN; ++q) fin = fin && isfinite(x[s][q]);
+                if (!fin) {
+                    if (values_out) values_out[i] = __int_as_float(0x7fc00000);
+                    continue;
+                }
+            }
+            if (values_out) values_out[i] = v0[s];
+            sv += v0[s]; sphi += phi[s]; spsi += psi[s];
+            if (a.target) {                                                   // metrics of model.evaluate(X1, ...), RP.py:215
+                const float ae = fabsf(tgt[s] - v1);
+                sae += ae;                                                    // 'mae'
+                sape += ae / fmaxf(fabsf(tgt[s]), 1e-7f);                     // 'mape' (Keras: |y - v| / max(|y|, epsilon), x 100 on the host)
+            }
         }
     }
     __shared__ double s_red[kFitThreads / 32][kPredictSums];
@@ -1636,10 +1656,10 @@ extern "C" int orp_fit_predict(const orp_fit_batch* b, const float* d_params, fl
     ORP_REQUIRE(d_params && d_sums && d_scratch, "null pointer");
     ORP_REQUIRE(a.n_seg == 1, "orp_fit_predict takes one segment per call");
     cudaStream_t st = (cudaStream_t)stream;
-    uint64_t want = (a.count + kFitThreads - 1) / kFitThreads;
-    // four resident blocks per SM (launch bounds), a whole number of waves: 592 blocks on B200, not 512 (3.46 per SM);
+    uint64_t want = (a.count + kPredS * kFitThreads - 1) / (kPredS * kFitThreads);
+    // the resident blocks of every SM (launch bounds), a whole number of waves: 444 blocks on B200;
     // their 5 partial sums each fit the 512 x kGsumLen doubles in front of the scratch header many times over
-    uint64_t cap = 4ull * (uint64_t)sm_count();
+    uint64_t cap = (uint64_t)kPredBlocksPerSM * (uint64_t)sm_count();
     if (cap * kPredictSums > kScrHeader) cap = kScrHeader / kPredictSums;
     const int grid = (int)(want < cap ? want : cap);
     double* partials = reinterpret_cast<double*>(d_scratch);
