@@ -6,6 +6,8 @@
 // result does not depend on scheduling (and matches on every launch bit for bit).
 #include "orp_common.h"
 
+#include <algorithm>
+#include <cstdlib>
 #include <mutex>
 
 namespace orp {
@@ -22,6 +24,9 @@ struct PayoffArgs {
     double* partials;                 // [gridDim.y][gridDim.x][2 * kPayChunk]
     double strikes[ORP_MAX_OPTIONS];
     int32_t cols[ORP_MAX_OPTIONS];
+    // bucket form only: strikes[] is sorted inside every chunk; slot[o] = position of that option in the caller's chunk
+    int8_t slot[ORP_MAX_OPTIONS];
+    double strike0;                   // the caller's option 0 (values_out)
 };
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -30,56 +35,76 @@ __device__ __forceinline__ double warp_sum(double v) {
     return v;
 }
 
-// Per-thread accumulators of one chunk of options.  The out-of-the-money tallies are integers (a thread sees far
-// fewer than 2^32 paths) and a NaN price is remembered as a flag instead of being added: per (path, option) the fp64
-// pipe then runs three instructions for a call / put (subtract, compare, add) and two for the floor.
+// Per-thread accumulators of one chunk of options.  Per (path, option) the loop runs ONE fp64 compare and, for the
+// paths in the money, one predicated fp64 add and one integer add: with d = S - K_ref (K_ref = the chunk's first
+// strike, one subtraction per path and column)
+//     call:  sum max(S - K, 0) = sum_{S > K} d - (K - K_ref) n_in          put:  (K - K_ref) n_in - sum_{S < K} d
+//     floor: sum (S > K ? S : K) = sum_{S > K} d + K_ref n_in + K (n - n_in)
+// are formed once per thread at the end; the in-the-money test is on S and K themselves (exact), the reference point
+// keeps the sums as small as the payoffs (no cancellation against the price level), and for the chunk's first option
+// (K = K_ref: the single-option pass of the backward loop) every bit equals the plain sum of S - K.  A NaN price is
+// remembered as a flag instead of being added.
 struct PayAcc {
     double sum[kPayChunk];
-    unsigned otm[kPayChunk], nan[kPayChunk];
+    unsigned n_in[kPayChunk], nan[kPayChunk];
+    unsigned below[kPayChunk];        // floor only: paths with S < s0 at the option's column (RP.py:89)
+    unsigned n;                       // paths seen
 };
 
+// One (path, option) pair: compare, and for a path in the money one predicated fp64 add and one predicated integer add
+// (written as PTX: from C the compiler forms the sum unconditionally and selects it back with two FSELs — six
+// instructions per pair instead of three, in a loop that ncu shows bound by instruction issue).
+template <int KIND>
+__device__ __forceinline__ void pay_pair(double s, double K, double d, double& sum, unsigned& n_in) {
+    if (KIND == ORP_PAYOFF_PUT)
+        asm("{\n\t.reg .pred p;\n\tsetp.lt.f64 p, %2, %3;\n\t@p add.f64 %0, %0, %4;\n\t@p add.u32 %1, %1, 1;\n\t}"
+            : "+d"(sum), "+r"(n_in) : "d"(s), "d"(K), "d"(d));
+    else
+        asm("{\n\t.reg .pred p;\n\tsetp.gt.f64 p, %2, %3;\n\t@p add.f64 %0, %0, %4;\n\t@p add.u32 %1, %1, 1;\n\t}"
+            : "+d"(sum), "+r"(n_in) : "d"(s), "d"(K), "d"(d));
+}
+
 // UU paths of one thread (all of them inside the path range) against the chunk's options.  KIND is a template
-// parameter: the payoff formula is fixed per launch, the option loop carries no dispatch.
+// parameter: the payoff formula is fixed per launch, the option loop carries no dispatch.  s_K: the chunk's strikes in
+// shared memory; new_col: bit k set when option k reads another column than option k - 1 (both fixed per block — read
+// from the launch arguments per option and iteration they cost twelve uniform-datapath instructions each).
 template <typename T, int KIND, int UU>
 __device__ __forceinline__ void payoff_paths(const PayoffArgs& a, const T* __restrict__ paths, uint64_t i, uint64_t stride,
-                                             int o_first, int n_here, bool write_values, PayAcc& acc) {
-    int last_col = -1;
-    double s[UU];
+                                             int o_first, int n_here, bool write_values, const double* s_K, unsigned new_col,
+                                             PayAcc& acc) {
+    double s[UU], d[UU];
     unsigned below[UU], any_nan = 0u;
+    const double k_ref = s_K[0];
 #pragma unroll
-    for (int u = 0; u < UU; ++u) { s[u] = 0.0; below[u] = 0u; }
+    for (int u = 0; u < UU; ++u) { s[u] = d[u] = 0.0; below[u] = 0u; }
+    acc.n += UU;
 #pragma unroll
     for (int k = 0; k < kPayChunk; ++k) {
         if (k < n_here) {                                   // uniform over the grid's y slice
-            const int col = a.cols[o_first + k];
-            if (col != last_col) {                          // options of a sweep arrive grouped by maturity column
+            if (new_col & (1u << k)) {                      // options of a sweep arrive grouped by maturity column
+                const int col = a.cols[o_first + k];
                 any_nan = 0u;
 #pragma unroll
                 for (int u = 0; u < UU; ++u) s[u] = (double)paths[(size_t)col * a.ld + i + u * stride];
 #pragma unroll
                 for (int u = 0; u < UU; ++u) {
+                    d[u] = s[u] - k_ref;
                     if (KIND == ORP_PAYOFF_FLOOR) below[u] = s[u] < a.s0 ? 1u : 0u;                // RP.py:89
                     else any_nan |= s[u] != s[u] ? 1u : 0u;
                 }
-                last_col = col;
             }
-            const double K = a.strikes[o_first + k];
+            const double K = s_K[k];
 #pragma unroll
             for (int u = 0; u < UU; ++u) {
-                double pay;
-                if (KIND == ORP_PAYOFF_FLOOR) {
-                    pay = s[u] > K ? s[u] : K;                                                     // RP.py:88 (np.where: NaN -> K)
-                    acc.otm[k] += below[u];
-                } else {
-                    const double d = KIND == ORP_PAYOFF_CALL ? s[u] - K : K - s[u];                // EO cell 8
-                    const bool in = d > 0.0;                                                       // false for NaN
-                    pay = in ? d : 0.0;
-                    acc.otm[k] += in ? 0u : 1u;
-                }
-                acc.sum[k] += pay;
+                // in the money (false for NaN): call S > K, put S < K (EO cell 8); floor: S > K keeps S (RP.py:88, np.where: NaN -> K)
+                pay_pair<KIND>(s[u], K, d[u], acc.sum[k], acc.n_in[k]);
+                if (KIND == ORP_PAYOFF_FLOOR) acc.below[k] += below[u];
                 if (k == 0 && write_values) {
-                    // np.maximum propagates NaN (the sums get it through the flag below)
-                    const double v = (KIND != ORP_PAYOFF_FLOOR && s[u] != s[u]) ? s[u] : pay;
+                    // option 0 is the chunk's reference: d = S - K.  np.maximum propagates NaN (the sums get it through the flag)
+                    const bool in = KIND == ORP_PAYOFF_PUT ? s[u] < K : s[u] > K;
+                    double v;
+                    if (KIND == ORP_PAYOFF_FLOOR) v = in ? s[u] : K;
+                    else v = s[u] != s[u] ? s[u] : (in ? (KIND == ORP_PAYOFF_CALL ? d[u] : -d[u]) : 0.0);
                     a.values_out[i + u * stride] = (float)(v * a.value_scale);
                 }
             }
@@ -96,9 +121,16 @@ __global__ void __launch_bounds__(kPayThreads, 4) payoff_partial_kernel(const Pa
     const T* __restrict__ paths = reinterpret_cast<const T*>(a.paths);
     const bool write_values = chunk == 0 && a.values_out != nullptr;
 
+    __shared__ double s_K[kPayChunk];
+    if (threadIdx.x < kPayChunk) s_K[threadIdx.x] = threadIdx.x < n_here ? a.strikes[o_first + threadIdx.x] : 0.0;
+    unsigned new_col = 1u;
+    for (int k = 1; k < n_here; ++k) new_col |= a.cols[o_first + k] != a.cols[o_first + k - 1] ? 1u << k : 0u;
+    __syncthreads();
+
     PayAcc acc;
 #pragma unroll
-    for (int k = 0; k < kPayChunk; ++k) { acc.sum[k] = 0.0; acc.otm[k] = acc.nan[k] = 0u; }
+    for (int k = 0; k < kPayChunk; ++k) { acc.sum[k] = 0.0; acc.n_in[k] = acc.nan[k] = acc.below[k] = 0u; }
+    acc.n = 0u;
 
     // four paths per thread and iteration: their column loads are independent, so four 8-byte requests per thread are
     // in flight (one per thread covered a quarter of the bandwidth-delay product of HBM); the ragged end of the range
@@ -107,15 +139,21 @@ __global__ void __launch_bounds__(kPayThreads, 4) payoff_partial_kernel(const Pa
     const uint64_t stride = (uint64_t)gridDim.x * kPayThreads;
     uint64_t i = (uint64_t)blockIdx.x * kPayThreads + threadIdx.x;
     for (; i + (U - 1) * stride < a.count; i += U * stride)
-        payoff_paths<T, KIND, U>(a, paths, i, stride, o_first, n_here, write_values, acc);
+        payoff_paths<T, KIND, U>(a, paths, i, stride, o_first, n_here, write_values, s_K, new_col, acc);
     for (; i < a.count; i += stride)
-        payoff_paths<T, KIND, 1>(a, paths, i, stride, o_first, n_here, write_values, acc);
+        payoff_paths<T, KIND, 1>(a, paths, i, stride, o_first, n_here, write_values, s_K, new_col, acc);
 
     double sum[kPayChunk], otm[kPayChunk];
+    const double k_ref = s_K[0];
 #pragma unroll
     for (int k = 0; k < kPayChunk; ++k) {
-        sum[k] = acc.nan[k] ? __longlong_as_double(0x7ff8000000000000ll) : acc.sum[k];
-        otm[k] = (double)acc.otm[k];
+        const double K = s_K[k], n_in = (double)acc.n_in[k], dk = K - k_ref;
+        double t;
+        if (KIND == ORP_PAYOFF_CALL) t = acc.sum[k] - dk * n_in;
+        else if (KIND == ORP_PAYOFF_PUT) t = dk * n_in - acc.sum[k];
+        else t = acc.sum[k] + k_ref * n_in + K * (double)(acc.n - acc.n_in[k]);
+        sum[k] = acc.nan[k] ? __longlong_as_double(0x7ff8000000000000ll) : t;
+        otm[k] = KIND == ORP_PAYOFF_FLOOR ? (double)acc.below[k] : (double)(acc.n - acc.n_in[k]);
     }
 
     __shared__ double s_red[kPayThreads / 32][2 * kPayChunk];
@@ -130,6 +168,103 @@ __global__ void __launch_bounds__(kPayThreads, 4) payoff_partial_kernel(const Pa
         double t = 0.0;
         for (int w = 0; w < kPayThreads / 32; ++w) t += s_red[w][threadIdx.x];
         a.partials[((size_t)chunk * gridDim.x + blockIdx.x) * (2 * kPayChunk) + threadIdx.x] = t;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sweep form: every chunk's options share ONE maturity column (a strike ladder per maturity, C4).  The strikes of a
+// chunk are sorted (calls and floors ascending, puts descending; the host does it and passes the original positions in
+// `slot`), so the options in the money for a path are exactly the first idx of them, idx = #{k : S > K_k} (puts: S <
+// K_k).  A path then costs eight compares and ONE accumulation — d = S - K_ref and a count into bucket idx of the
+// thread's own nine buckets in shared memory — instead of eight compare/add/select groups (ncu on the pair loop: 395
+// instructions per four paths and eight options, issue slots 77 % busy, DRAM 27 %).  At the end
+//     sum_{S > K_k} d = sum_{j > k} bucket[j],   n_in(k) = sum_{j > k} count[j]
+// and the per-option sums follow by the formulas of PayAcc.  The in-the-money sets are exact (compares on S and K
+// themselves), so the out-of-the-money tallies equal those of the pair loop; the sums differ from it by fp64 rounding.
+constexpr int kBuckets = kPayChunk + 1;
+
+template <typename T, int KIND>
+__global__ void __launch_bounds__(kPayThreads, 4) payoff_bucket_kernel(const PayoffArgs a) {
+    const int chunk = blockIdx.y;
+    const int o_first = chunk * kPayChunk;
+    const int n_here = min(kPayChunk, a.n_opt - o_first);
+    const T* __restrict__ col = reinterpret_cast<const T*>(a.paths) + (size_t)a.cols[o_first] * a.ld;
+    const bool write_values = chunk == 0 && a.values_out != nullptr;
+
+    __shared__ double s_bd[kBuckets][kPayThreads];
+    __shared__ unsigned s_bc[kBuckets][kPayThreads];
+#pragma unroll
+    for (int j = 0; j < kBuckets; ++j) { s_bd[j][threadIdx.x] = 0.0; s_bc[j][threadIdx.x] = 0u; }
+    // never-in-the-money padding behind the last option of a short chunk
+    const double pad = __longlong_as_double(KIND == ORP_PAYOFF_PUT ? 0xfff0000000000000ll : 0x7ff0000000000000ll);
+    double K[kPayChunk];
+#pragma unroll
+    for (int k = 0; k < kPayChunk; ++k) K[k] = k < n_here ? a.strikes[o_first + k] : pad;
+    const double k_ref = K[0];
+    unsigned n = 0u, below = 0u, any_nan = 0u;
+
+    auto one_path = [&](double sv, uint64_t i) {
+        unsigned idx = 0u;
+#pragma unroll
+        for (int k = 0; k < kPayChunk; ++k) idx += (KIND == ORP_PAYOFF_PUT ? sv < K[k] : sv > K[k]) ? 1u : 0u;
+        s_bd[idx][threadIdx.x] += sv - k_ref;
+        s_bc[idx][threadIdx.x] += 1u;
+        if (KIND == ORP_PAYOFF_FLOOR) below += sv < a.s0 ? 1u : 0u;                            // RP.py:89
+        else any_nan |= sv != sv ? 1u : 0u;
+        if (write_values) {                                 // the caller's option 0; np.maximum propagates NaN
+            const double K0 = a.strike0;
+            const bool in = KIND == ORP_PAYOFF_PUT ? sv < K0 : sv > K0;
+            double v;
+            if (KIND == ORP_PAYOFF_FLOOR) v = in ? sv : K0;
+            else v = sv != sv ? sv : (in ? (KIND == ORP_PAYOFF_CALL ? sv - K0 : K0 - sv) : 0.0);
+            a.values_out[i] = (float)(v * a.value_scale);
+        }
+    };
+
+    constexpr int U = 4;                                    // four independent column loads per thread in flight
+    const uint64_t stride = (uint64_t)gridDim.x * kPayThreads;
+    uint64_t i = (uint64_t)blockIdx.x * kPayThreads + threadIdx.x;
+    for (; i + (U - 1) * stride < a.count; i += U * stride) {
+        double sv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) sv[u] = (double)col[i + u * stride];
+#pragma unroll
+        for (int u = 0; u < U; ++u) one_path(sv[u], i + u * stride);
+        n += U;
+    }
+    for (; i < a.count; i += stride) { one_path((double)col[i], i); n += 1u; }
+
+    // buckets -> per-option sums (sorted positions), then the same block reduction as the pair form
+    double sum[kPayChunk], otm[kPayChunk];
+    double tail_d = 0.0;
+    unsigned tail_c = 0u;
+#pragma unroll
+    for (int k = kPayChunk - 1; k >= 0; --k) {
+        tail_d += s_bd[k + 1][threadIdx.x];
+        tail_c += s_bc[k + 1][threadIdx.x];
+        const double n_in = (double)tail_c, dk = K[k] - k_ref;
+        double t;
+        if (KIND == ORP_PAYOFF_CALL) t = tail_d - dk * n_in;
+        else if (KIND == ORP_PAYOFF_PUT) t = dk * n_in - tail_d;
+        else t = tail_d + k_ref * n_in + K[k] * (double)(n - tail_c);
+        if (k >= n_here) t = 0.0;                           // padding: keep inf * 0 out of the partials
+        sum[k] = (KIND != ORP_PAYOFF_FLOOR && any_nan) ? __longlong_as_double(0x7ff8000000000000ll) : t;
+        otm[k] = KIND == ORP_PAYOFF_FLOOR ? (double)below : (double)(n - tail_c);
+    }
+
+    __shared__ double s_red[kPayThreads / 32][2 * kPayChunk];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < kPayChunk; ++k) {
+        const double a_ = warp_sum(sum[k]), b_ = warp_sum(otm[k]);
+        if (lane == 0) { s_red[warp][2 * k] = a_; s_red[warp][2 * k + 1] = b_; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 2 * kPayChunk && (threadIdx.x >> 1) < n_here) {
+        double t = 0.0;
+        for (int w = 0; w < kPayThreads / 32; ++w) t += s_red[w][threadIdx.x];
+        const int pos = a.slot[o_first + (threadIdx.x >> 1)];                  // back to the caller's order inside the chunk
+        a.partials[((size_t)chunk * gridDim.x + blockIdx.x) * (2 * kPayChunk) + 2 * pos + (threadIdx.x & 1)] = t;
     }
 }
 
@@ -152,8 +287,9 @@ __global__ void __launch_bounds__(kFinalThreads) payoff_final_kernel(const doubl
 
 static int payoff_blocks() { return 4 * sm_count(); }        // four resident blocks per SM (launch bounds): whole waves
 
-static void launch_payoff_partial(int dtype, int kind, dim3 grid, cudaStream_t st, const PayoffArgs& a) {
-#define ORP_PAY(T, KIND) payoff_partial_kernel<T, KIND><<<grid, kPayThreads, 0, st>>>(a)
+static void launch_payoff_partial(int dtype, int kind, dim3 grid, cudaStream_t st, const PayoffArgs& a, bool buckets) {
+#define ORP_PAY(T, KIND) do { if (buckets) payoff_bucket_kernel<T, KIND><<<grid, kPayThreads, 0, st>>>(a); \
+                              else payoff_partial_kernel<T, KIND><<<grid, kPayThreads, 0, st>>>(a); } while (0)
     if (dtype == ORP_F64) {
         if (kind == ORP_PAYOFF_CALL) ORP_PAY(double, ORP_PAYOFF_CALL);
         else if (kind == ORP_PAYOFF_PUT) ORP_PAY(double, ORP_PAYOFF_PUT);
@@ -169,6 +305,27 @@ static void launch_payoff_partial(int dtype, int kind, dim3 grid, cudaStream_t s
 }  // namespace orp
 
 using namespace orp;
+
+// Bucket form (payoff_bucket_kernel) for a call of several options whose chunks each read ONE column: sorts the strikes
+// inside every chunk (calls / floors ascending, puts descending) and records where each came from.
+static bool prepare_buckets(PayoffArgs& a) {
+    if (a.n_opt < 2 || getenv("ORP_B200_NO_BUCKETS")) return false;
+    for (int k = 1; k < a.n_opt; ++k)
+        if (k % kPayChunk != 0 && a.cols[k] != a.cols[k - 1]) return false;
+    a.strike0 = a.strikes[0];
+    for (int o = 0; o < a.n_opt; o += kPayChunk) {
+        const int n = std::min(kPayChunk, a.n_opt - o);
+        int order[kPayChunk];
+        for (int k = 0; k < n; ++k) order[k] = k;
+        std::stable_sort(order, order + n, [&](int x, int y) {
+            return a.kind == ORP_PAYOFF_PUT ? a.strikes[o + x] > a.strikes[o + y] : a.strikes[o + x] < a.strikes[o + y];
+        });
+        double sorted[kPayChunk];
+        for (int k = 0; k < n; ++k) { sorted[k] = a.strikes[o + order[k]]; a.slot[o + k] = (int8_t)order[k]; }
+        for (int k = 0; k < n; ++k) a.strikes[o + k] = sorted[k];
+    }
+    return true;
+}
 
 extern "C" uint64_t orp_payoff_scratch_bytes(int n_opt) {
     if (n_opt < 1) n_opt = 1;
@@ -203,7 +360,8 @@ extern "C" int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, ui
     if ((uint64_t)gx > want) gx = (int)want;
     cudaStream_t st = (cudaStream_t)stream;
     dim3 grid(gx, chunks);
-    launch_payoff_partial(dtype, kind, grid, st, a);
+    for (int k = 0; k < n_opt; ++k) ORP_REQUIRE(strikes[k] == strikes[k], "strike %d is NaN", k);
+    launch_payoff_partial(dtype, kind, grid, st, a, prepare_buckets(a));
     ORP_LAUNCH_CHECK("payoff_partial_kernel");
     payoff_final_kernel<<<(2 * n_opt * 32 + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, st>>>(a.partials, gx, n_opt, d_sums, d_otm);
     ORP_LAUNCH_CHECK("payoff_final_kernel");
@@ -277,7 +435,7 @@ extern "C" int orp_payoff_reduce_noalloc(const void* d_paths, int dtype, uint64_
     // Nothing in the array has to start at zero: every block of this launch overwrites its own 16 slots and the
     // second kernel reads exactly those gx blocks, so what an earlier call left behind is never looked at.
     dim3 grid(gx, 1);
-    launch_payoff_partial(dtype, kind, grid, st, a);
+    launch_payoff_partial(dtype, kind, grid, st, a, false);
     ORP_LAUNCH_CHECK("payoff_partial_kernel (noalloc)");
     payoff_final_kernel<<<(2 * n_opt * 32 + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, st>>>(partials, gx, n_opt, d_sums, d_otm);
     ORP_LAUNCH_CHECK("payoff_final_kernel (noalloc)");

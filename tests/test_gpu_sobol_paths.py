@@ -303,3 +303,54 @@ def test_fused_sweep_c4_shape_and_errors(cuda):
         orp_b200.payoff_sums_fused("gbm_log", p, [100.0], [D + 1], m=m, steps=D, device=cuda)
     with pytest.raises(ValueError):
         orp_b200.payoff_sums_fused("gbm_log", p, np.full(65, 100.0), np.full(65, D), m=m, steps=D, device=cuda)
+
+
+@pytest.mark.parametrize("kind", ["call", "put", "floor"])
+@pytest.mark.parametrize("dtype", ["float64", "float32"])
+def test_strike_ladder_bucket_form_equals_the_pair_form_and_numpy(cuda, kind, dtype, monkeypatch):
+    """Several options on ONE column go through payoff_bucket_kernel (strikes sorted per chunk, one accumulation per
+    path into the bucket 'number of options in the money'): unsorted strikes with ties, a short last chunk, strikes
+    outside the price range, NaN and +-inf prices — against NumPy (sums 1e-12, out-of-the-money counts exact) and against
+    the pair form (ORP_B200_NO_BUCKETS)."""
+    import torch
+    import orp_b200
+    rng = np.random.default_rng(17)
+    n = 50_003
+    col = (100.0 * np.exp(0.3 * rng.standard_normal(n))).astype(dtype)
+    tm = torch.from_numpy(np.stack([np.full(n, 100.0, dtype=dtype), col])).to(cuda)
+    strikes = np.array([120.0, 80.0, 100.0, 100.0, 95.5, 300.0, 1.0, 110.0, 90.0, 1e6, 100.25])      # 8 + 3
+    cols = np.ones(strikes.size, dtype=np.int64)
+
+    def numpy_ref(c):
+        c = c.astype(np.float64)
+        out_s, out_o = [], []
+        for K in strikes:
+            pay = opaths.payoff(c, K, kind)
+            out_s.append(pay.sum())
+            out_o.append(np.count_nonzero(c < 100.0) if kind == "floor" else np.count_nonzero(~(pay > 0)))
+        return np.array(out_s), np.array(out_o, dtype=np.float64)
+
+    sums, otm = orp_b200.payoff_sums(tm, strikes, cols, kind, s0=100.0)
+    rs, ro = numpy_ref(col)
+    np.testing.assert_allclose(sums.cpu().numpy(), rs, rtol=1e-12)
+    assert np.array_equal(otm.cpu().numpy(), ro)
+    vals = torch.empty(n, dtype=torch.float32, device=cuda)
+    orp_b200.payoff_sums(tm, strikes, cols, kind, s0=100.0, values_out=vals, value_scale=0.01)
+    np.testing.assert_allclose(vals.cpu().numpy(), (opaths.payoff(col.astype(np.float64), strikes[0], kind) * 0.01).astype(np.float32), rtol=1e-6)
+    monkeypatch.setenv("ORP_B200_NO_BUCKETS", "1")
+    sums2, otm2 = orp_b200.payoff_sums(tm, strikes, cols, kind, s0=100.0)
+    monkeypatch.delenv("ORP_B200_NO_BUCKETS")
+    np.testing.assert_allclose(sums.cpu().numpy(), sums2.cpu().numpy(), rtol=1e-12)
+    assert np.array_equal(otm.cpu().numpy(), otm2.cpu().numpy())
+    # non-finite prices: same rules as the single-option pass (np.maximum propagates NaN; np.where(NaN > K, ., K) = K)
+    bad = col.copy()
+    bad[[5, 77, 4000]] = [np.nan, np.inf, -np.inf]
+    tm_bad = torch.from_numpy(np.stack([np.full(n, 100.0, dtype=dtype), bad])).to(cuda)
+    sums3, otm3 = orp_b200.payoff_sums(tm_bad, strikes, cols, kind, s0=100.0)
+    with np.errstate(invalid="ignore"):
+        rs3, ro3 = numpy_ref(bad)
+    got = sums3.cpu().numpy()
+    assert np.array_equal(np.isnan(got), np.isnan(rs3)) and np.array_equal(np.isinf(got), np.isinf(rs3))
+    fin = np.isfinite(rs3)
+    np.testing.assert_allclose(got[fin], rs3[fin], rtol=1e-12)
+    assert np.array_equal(otm3.cpu().numpy(), ro3)
