@@ -36,7 +36,7 @@ __device__ __forceinline__ double warp_sum(double v) {
 }
 
 // Per-thread accumulators of one chunk of options.  Per (path, option) the loop runs ONE fp64 compare and, for the
-// paths in the money, one predicated fp64 add and one integer add: with d = S - K_ref (K_ref = the chunk's first
+// paths in the money, one fp64 add and one integer add: with d = S - K_ref (K_ref = the chunk's first
 // strike, one subtraction per path and column)
 //     call:  sum max(S - K, 0) = sum_{S > K} d - (K - K_ref) n_in          put:  (K - K_ref) n_in - sum_{S < K} d
 //     floor: sum (S > K ? S : K) = sum_{S > K} d + K_ref n_in + K (n - n_in)
@@ -51,17 +51,13 @@ struct PayAcc {
     unsigned n;                       // paths seen
 };
 
-// One (path, option) pair: compare, and for a path in the money one predicated fp64 add and one predicated integer add
-// (written as PTX: from C the compiler forms the sum unconditionally and selects it back with two FSELs — six
-// instructions per pair instead of three, in a loop that ncu shows bound by instruction issue).
+// One (path, option) pair.  (ptxas turns the conditional fp64 add into add + compare + two selects — also when it is
+// written as a predicated add in PTX — so a pair costs five to six instructions; strike ladders avoid the per-option
+// work altogether, see payoff_bucket_kernel.)
 template <int KIND>
 __device__ __forceinline__ void pay_pair(double s, double K, double d, double& sum, unsigned& n_in) {
-    if (KIND == ORP_PAYOFF_PUT)
-        asm("{\n\t.reg .pred p;\n\tsetp.lt.f64 p, %2, %3;\n\t@p add.f64 %0, %0, %4;\n\t@p add.u32 %1, %1, 1;\n\t}"
-            : "+d"(sum), "+r"(n_in) : "d"(s), "d"(K), "d"(d));
-    else
-        asm("{\n\t.reg .pred p;\n\tsetp.gt.f64 p, %2, %3;\n\t@p add.f64 %0, %0, %4;\n\t@p add.u32 %1, %1, 1;\n\t}"
-            : "+d"(sum), "+r"(n_in) : "d"(s), "d"(K), "d"(d));
+    const bool in = KIND == ORP_PAYOFF_PUT ? s < K : s > K;
+    if (in) { sum += d; n_in += 1u; }
 }
 
 // UU paths of one thread (all of them inside the path range) against the chunk's options.  KIND is a template
