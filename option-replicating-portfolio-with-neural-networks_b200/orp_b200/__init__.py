@@ -9,7 +9,7 @@ from .sobol import SobolEngine, sobol_uint32, sobol_normal, ndtri_u32          #
 from .paths import (simulate_paths, payoff_sums, price_european, bond_curve,   # noqa: F401
                     n_time_steps_of, reduction_of, shard_range, bridge_schedule_host,
                     payoff_sums_fused, price_european_fused)
-from .fit import fit_replication, ReplicationNet, Optimizer, init_params, n_params, scale_column   # noqa: F401
+from .fit import fit_replication, ReplicationNet, Optimizer, init_params, n_params, scale_column, release_peers   # noqa: F401
 from .risk import quantiles, survivors                                                    # noqa: F401
 from .calibrate import CIRParams, estimate_CIR_params                          # noqa: F401
 from . import dist                                                             # noqa: F401
