@@ -355,9 +355,13 @@ extern "C" int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, ui
     if (gx > 1024) gx = 1024;
     if ((uint64_t)gx > want) gx = (int)want;
     cudaStream_t st = (cudaStream_t)stream;
-    dim3 grid(gx, chunks);
     for (int k = 0; k < n_opt; ++k) ORP_REQUIRE(strikes[k] == strikes[k], "strike %d is NaN", k);
-    launch_payoff_partial(dtype, kind, grid, st, a, prepare_buckets(a));
+    const bool buckets = prepare_buckets(a);
+    // strike ladders: ONE wave of blocks over all chunks together (each block zeroes and folds 18 bucket columns and runs
+    // sixteen warp reductions: with a full grid per chunk those fixed costs were paid eight times per SM slot)
+    if (buckets && !getenv("ORP_B200_BUCKET_FULL_GRID")) gx = std::max(1, std::min(gx, (payoff_blocks() + chunks - 1) / chunks));
+    dim3 grid(gx, chunks);
+    launch_payoff_partial(dtype, kind, grid, st, a, buckets);
     ORP_LAUNCH_CHECK("payoff_partial_kernel");
     payoff_final_kernel<<<(2 * n_opt * 32 + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, st>>>(a.partials, gx, n_opt, d_sums, d_otm);
     ORP_LAUNCH_CHECK("payoff_final_kernel");
