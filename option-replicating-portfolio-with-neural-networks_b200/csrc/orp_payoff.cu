@@ -357,9 +357,12 @@ extern "C" int orp_payoff_reduce(const void* d_paths, int dtype, uint64_t ld, ui
     cudaStream_t st = (cudaStream_t)stream;
     for (int k = 0; k < n_opt; ++k) ORP_REQUIRE(strikes[k] == strikes[k], "strike %d is NaN", k);
     const bool buckets = prepare_buckets(a);
-    // strike ladders: ONE wave of blocks over all chunks together (each block zeroes and folds 18 bucket columns and runs
-    // sixteen warp reductions: with a full grid per chunk those fixed costs were paid eight times per SM slot)
-    if (buckets && !getenv("ORP_B200_BUCKET_FULL_GRID")) gx = std::max(1, std::min(gx, (payoff_blocks() + chunks - 1) / chunks));
+    // strike ladders with short blocks (< 2^16 paths each on a full grid per chunk): ONE wave of blocks over all chunks
+    // together — each block zeroes and folds 18 bucket columns and runs sixteen warp reductions, fixed costs that a full
+    // grid per chunk pays eight times per SM slot (64 options: 298 -> 288 us at 2^24 paths; at 2^26 the full grid stays,
+    // 1032 against 1072 us)
+    if (buckets && count / (uint64_t)gx < (1ull << 16) && !getenv("ORP_B200_BUCKET_FULL_GRID"))
+        gx = std::max(1, std::min(gx, (payoff_blocks() + chunks - 1) / chunks));
     dim3 grid(gx, chunks);
     launch_payoff_partial(dtype, kind, grid, st, a, buckets);
     ORP_LAUNCH_CHECK("payoff_partial_kernel");
