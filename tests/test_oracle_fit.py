@@ -81,3 +81,30 @@ def test_price_and_hedge_at_t0_are_the_notebooks_within_the_seed_spread(eo_run):
     assert v0 > disc                                            # the method over-prices, there (8 %) and here
     assert abs(res["phi0"] - log["phi0"]) < 0.02 and abs(res["psi0"] - log["psi0"]) < 0.02
     assert abs(res["phi0"] + res["psi0"] - 1) < 1e-6            # psi = 1 - phi (EO cell 12)
+
+
+def test_batch_order_identity_equals_index_order_and_a_permutation_changes_the_steps():
+    """``batch_order`` (the step make-up handed to the oracle by the virtual-shard test of the CUDA path): the identity
+    order is the default index order bit for bit; the virtual-shard order visits the same samples per epoch in other
+    steps, so the trajectory differs while the first epoch's total sample set does not."""
+    rng = np.random.default_rng(4)
+    n, D = 4096, 2
+    z = rng.standard_normal((n, D))
+    S = np.empty((n, D + 1))
+    S[:, 0] = 100.0
+    for t in range(D):
+        S[:, t + 1] = S[:, t] * np.exp((0.05 - 0.02) / 12 + 0.2 * np.sqrt(1 / 12) * z[:, t])
+    bond = np.exp(0.05 * np.arange(D + 1) / 12)
+    y = np.maximum(S[:, -1] - 100.0, 0.0) / 100.0
+    kw = dict(net="eo", scale=100.0, epochs_first=3, epochs_next=2, patience_first=3, patience_next=2, batch_size=n // 8,
+              shuffle_seed=None)
+    a = ofit.backward_replication(S, bond, y, **kw)
+    b = ofit.backward_replication(S, bond, y, batch_order=np.arange(n), **kw)
+    assert a["V0"] == b["V0"] and np.array_equal(a["params"], b["params"])
+    V, spe = 8, 8
+    seg = n // V
+    per = seg // spe
+    order = np.concatenate([np.arange(v * seg + k * per, v * seg + (k + 1) * per) for k in range(spe) for v in range(V)])
+    assert np.array_equal(np.sort(order), np.arange(n))
+    c = ofit.backward_replication(S, bond, y, batch_order=order, **kw)
+    assert not np.array_equal(a["params"], c["params"]) and abs(c["V0"] / a["V0"] - 1) < 0.05
